@@ -1,0 +1,146 @@
+// oracle/ref_gpu_driver.cu — replaces the reference's main.cu (main.cu:25-94) as the entry point
+// of the reference's OWN CUDA program, linked against the reference's unmodified objects
+// (parse, config_utils, lbvh_utils, lbvh_builder, bvh_traversal, struct, helper, draw).
+// TEST / BASELINE INFRASTRUCTURE ONLY.  It calls the same sequence main.cu calls and adds:
+//   --bounds computed   store the bounding box that parse.cpp accumulates and drops (F1)
+//   --dump PREFIX       write codes / refs / nodes (reference layouts) and the RGBA image
+//   --ids               closest-hit ids of the exact-centre primary rays via material tags
+//   --w/--h/--aa        override the scene's png / aa lines;  --repeat N  re-time build and render
+// It prints one JSON object on the last stdout line.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "config.hpp"
+#include "config_utils.cuh"
+#include "draw.cuh"
+#include "parse.hpp"
+#include "lbvh_builder.cuh"
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "CUDA %s at %d: %s\n", #x, __LINE__, cudaGetErrorString(e_)); exit(2); } } while (0)
+
+static void write_file(const std::string& p, const void* d, size_t n) {
+  FILE* f = fopen(p.c_str(), "wb"); if (!f) { perror(p.c_str()); exit(3); }
+  fwrite(d, 1, n, f); fclose(f);
+}
+
+__global__ void id_kernel(int* out_kind, unsigned* out_pid, float* out_t, int W, int H, RawConfig* cfg) {
+  int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= W * H) return;
+  curandState state; curand_init(1234, tid, 0, &state);
+  Ray ray((float)(tid % W), (float)(tid / W), &state, cfg);
+  ObjectInfo o = hitNearest(ray, cfg);
+  out_kind[tid] = o.isHit ? (int)o.mat.color.r : 0;
+  out_pid[tid] = o.isHit ? ((unsigned)o.mat.color.g | ((unsigned)o.mat.color.b << 16)) : 0u;
+  out_t[tid] = o.isHit ? o.distance : INFINITY;
+}
+
+static double now() { return std::chrono::duration<double>(std::chrono::high_resolution_clock::now().time_since_epoch()).count(); }
+
+int main(int argc, char** argv) {
+  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds computed|shipped] [--dump P] [--ids] [--w W --h H --aa A] [--repeat N]\n", argv[0]); return 1; }
+  bool computed = false, ids = false; std::string dump; int W = -1, H = -1, AA = -1, repeat = 1;
+  for (int i = 2; i < argc; i++) {
+    std::string a = argv[i];
+    if (a == "--bounds" && i + 1 < argc) computed = std::string(argv[++i]) == "computed";
+    else if (a == "--dump" && i + 1 < argc) dump = argv[++i];
+    else if (a == "--ids") ids = true;
+    else if (a == "--w" && i + 1 < argc) W = atoi(argv[++i]);
+    else if (a == "--h" && i + 1 < argc) H = atoi(argv[++i]);
+    else if (a == "--aa" && i + 1 < argc) AA = atoi(argv[++i]);
+    else if (a == "--repeat" && i + 1 < argc) repeat = atoi(argv[++i]);
+  }
+  double t0 = now();
+  StlConfig stl;
+  parseInput(argv, stl);
+  double t_parse = now() - t0;
+  if (W > 0) stl.width = W; if (H > 0) stl.height = H; if (AA >= 0) stl.aa = AA;
+  if (computed) {  // what parse.cpp:147-155,193-200 accumulates into its local and never stores
+    AABB b;
+    auto acc = [&](const AABB& p) {
+      b.x.min = fminf(b.x.min, p.x.min); b.x.max = fmaxf(b.x.max, p.x.max);
+      b.y.min = fminf(b.y.min, p.y.min); b.y.max = fmaxf(b.y.max, p.y.max);
+      b.z.min = fminf(b.z.min, p.z.min); b.z.max = fmaxf(b.z.max, p.z.max);
+    };
+    for (auto& s : stl.host_spheres_data) { vec3 r(s.r, s.r, s.r); acc(AABB(s.c - r, s.c + r)); }
+    for (auto& t : stl.host_triangles_data) acc(AABB(t.p0, t.p1, t.p2));
+    stl.scene_bounds_host = b;
+  }
+  CK(cudaFree(0));
+  std::vector<double> build_ms, build_wall_ms, render_s;
+  RawConfig rc; RawConfig* d_rc = nullptr; pixel_t* d_img = nullptr;
+  const int N = (int)stl.host_primitive_references.size();
+  const size_t npx = (size_t)stl.width * stl.height;
+  CK(cudaDeviceSetLimit(cudaLimitStackSize, 64 * 1024));  // main.cu:64
+  for (int rep = 0; rep < repeat; rep++) {
+    if (rep > 0) { freeRawConfigDeviceMemory(rc); CK(cudaFree(d_rc)); CK(cudaFree(d_img)); }
+    initRawConfigFromStl(stl, rc);
+    copyConfigDataToDevice(stl, rc);
+    CK(cudaDeviceSynchronize());
+    double tb = now();
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventRecord(e0));
+    if (N > 0) build_lbvh_karas(rc, 30);  // main.cu:44-46
+    CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+    build_ms.push_back(ms); build_wall_ms.push_back((now() - tb) * 1e3);
+    CK(cudaMalloc(&d_rc, sizeof(RawConfig))); CK(cudaMemcpy(d_rc, &rc, sizeof(RawConfig), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&d_img, npx * sizeof(pixel_t))); CK(cudaMemset(d_img, 0, npx * sizeof(pixel_t)));
+    CK(cudaDeviceSynchronize());
+    double tr = now();
+    render(d_img, stl.width, stl.height, stl.aa, d_rc);  // main.cu:67
+    CK(cudaDeviceSynchronize());
+    render_s.push_back(now() - tr);
+    CK(cudaPeekAtLastError());
+  }
+  if (!dump.empty()) {
+    std::vector<unsigned> codes((size_t)N); std::vector<PrimitiveReference> refs((size_t)N); std::vector<LBVHNode> nodes((size_t)rc.num_lbvh_nodes);
+    CK(cudaMemcpy(codes.data(), rc.d_morton_codes, N * sizeof(unsigned), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(refs.data(), rc.d_primitive_references, N * sizeof(PrimitiveReference), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(nodes.data(), rc.d_lbvh_nodes, nodes.size() * sizeof(LBVHNode), cudaMemcpyDeviceToHost));
+    std::vector<pixel_t> img(npx);
+    CK(cudaMemcpy(img.data(), d_img, npx * sizeof(pixel_t), cudaMemcpyDeviceToHost));
+    write_file(dump + ".codes.u32", codes.data(), codes.size() * 4);
+    write_file(dump + ".refs.i32", refs.data(), refs.size() * 8);
+    write_file(dump + ".nodes.bin", nodes.data(), nodes.size() * sizeof(LBVHNode));
+    write_file(dump + ".rgba", img.data(), img.size() * 4);
+  }
+  if (ids && !dump.empty()) {
+    StlConfig tagged = stl;
+    auto tag = [](Materials& m, int kind, unsigned id) { m.color = RGB((float)kind, (float)(id & 0xFFFF), (float)(id >> 16)); };
+    for (size_t i = 0; i < tagged.host_spheres_data.size(); i++) tag(tagged.host_spheres_data[i].mat, 1, (unsigned)i);
+    for (size_t i = 0; i < tagged.host_triangles_data.size(); i++) tag(tagged.host_triangles_data[i].mat, 2, (unsigned)i);
+    for (size_t i = 0; i < tagged.plane_data.size(); i++) tag(tagged.plane_data[i].mat, 3, (unsigned)i);
+    RawConfig rt; initRawConfigFromStl(tagged, rt); copyConfigDataToDevice(tagged, rt);
+    // same tree and same sorted reference list as the real build
+    CK(cudaMemcpy(rt.d_primitive_references, rc.d_primitive_references, N * sizeof(PrimitiveReference), cudaMemcpyDeviceToDevice));
+    rt.d_lbvh_nodes = rc.d_lbvh_nodes; rt.num_lbvh_nodes = rc.num_lbvh_nodes;
+    RawConfig* d_rt; CK(cudaMalloc(&d_rt, sizeof(RawConfig))); CK(cudaMemcpy(d_rt, &rt, sizeof(RawConfig), cudaMemcpyHostToDevice));
+    int* dk; unsigned* dp; float* dt;
+    CK(cudaMalloc(&dk, npx * 4)); CK(cudaMalloc(&dp, npx * 4)); CK(cudaMalloc(&dt, npx * 4));
+    id_kernel<<<(unsigned)((npx + 127) / 128), 128>>>(dk, dp, dt, stl.width, stl.height, d_rt);
+    CK(cudaDeviceSynchronize());
+    std::vector<int> hk(npx); std::vector<unsigned> hp(npx); std::vector<float> ht(npx);
+    CK(cudaMemcpy(hk.data(), dk, npx * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(hp.data(), dp, npx * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(ht.data(), dt, npx * 4, cudaMemcpyDeviceToHost));
+    std::vector<int> spos(stl.host_spheres_data.size()), tpos(stl.host_triangles_data.size());
+    for (size_t i = 0; i < stl.host_primitive_references.size(); i++) {
+      auto& r = stl.host_primitive_references[i];
+      if (r.type == PrimitiveType::SPHERE) spos[r.id_in_type_array] = (int)i; else tpos[r.id_in_type_array] = (int)i;
+    }
+    std::vector<int> out(npx);
+    for (size_t i = 0; i < npx; i++) out[i] = hk[i] == 1 ? spos[hp[i]] : hk[i] == 2 ? tpos[hp[i]] : hk[i] == 3 ? -2 - (int)hp[i] : -1;
+    write_file(dump + ".ids.i32", out.data(), npx * 4);
+    write_file(dump + ".t.f32", ht.data(), npx * 4);
+  }
+  printf("\n{\"n\": %d, \"w\": %d, \"h\": %d, \"aa\": %d, \"bounds\": \"%s\", \"parse_s\": %.6f, \"build_ms\": [", N, stl.width, stl.height, stl.aa,
+         computed ? "computed" : "shipped", t_parse);
+  for (size_t i = 0; i < build_ms.size(); i++) printf("%s%.4f", i ? ", " : "", build_ms[i]);
+  printf("], \"build_wall_ms\": [");
+  for (size_t i = 0; i < build_wall_ms.size(); i++) printf("%s%.4f", i ? ", " : "", build_wall_ms[i]);
+  printf("], \"render_s\": [");
+  for (size_t i = 0; i < render_s.size(); i++) printf("%s%.6f", i ? ", " : "", render_s[i]);
+  printf("]}\n");
+  return 0;
+}
