@@ -1,0 +1,297 @@
+// build_tree.cu — hierarchy + AABB refit (K3..K6) and rt_build_lbvh.
+//
+// Replaces initialize_leaf_nodes_kernel, generate_internal_nodes_karas_kernel,
+// initialize_visited_counters_kernel and set_aabb_kernel_adapted (src/lbvh_builder.cu:59-71,224-322,
+// 389-397,324-387) and the orchestration in build_lbvh_karas (:401-521).
+//
+// The tree is the binary radix tree of Karras 2012 over the augmented keys (code, sorted position):
+// delta(i,j) = clz(code_i ^ code_j), or bits + clz(i ^ j) for equal codes (lbvh_builder.cu:76-101).
+// Two builders produce the same tree:
+//  * default, fused bottom-up (Apetrei 2014): one thread per leaf climbs; at every step the node
+//    [l,r] joins the neighbour it shares the longer prefix with (delta(r,r+1) > delta(l-1,l) ⇒ it is
+//    the LEFT child of the node that splits after r, else the RIGHT child of the node that splits
+//    after l-1).  The first child to arrive deposits its 32-byte half (box + reference) in the
+//    parent's slot and leaves; the second unions the two boxes and continues.  Topology and refit
+//    are one kernel, one atomic per node, and only adjacent deltas are evaluated.  Nodes are stored
+//    at slot = split position; the reference's numbering (internal index = split of the parent for a
+//    left child, split+1 for a right child, root 0) is recovered on export.
+//  * RT_BUILD_TOPDOWN: per-node range and split search exactly as the reference does it, in the
+//    reference's numbering, followed by the atomic bottom-up refit with the fence the reference
+//    lacks.
+#include "build.cuh"
+
+namespace {
+
+template <typename KeyT>
+struct Delta {
+  const KeyT* keys; int n;
+  __device__ inline int adj(int i) const {  // delta(i, i+1); -1 outside (lbvh_builder.cu:84-87)
+    if (i < 0 || i >= n - 1) return -1;
+    return pair(i, i + 1);
+  }
+  __device__ inline int pair(int a, int b) const {
+    if (a < 0 || a >= n || b < 0 || b >= n) return -1;
+    KeyT ka = keys[a], kb = keys[b];
+    if (ka == kb) return (int)(8 * sizeof(KeyT)) + __clz((unsigned)a ^ (unsigned)b);  // lbvh_builder.cu:92-98
+    return sizeof(KeyT) == 4 ? __clz((unsigned)(ka ^ kb)) : __clzll((long long)(ka ^ kb));
+  }
+};
+
+__device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref) {
+  float4* h = nodes + 4 * (size_t)slot + 2 * side;
+  __stcg(h, make_float4(b.xmin, b.ymin, b.zmin, b.xmax));
+  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), 0.f));
+}
+__device__ inline void load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
+  const float4* h = nodes + 4 * (size_t)slot + 2 * side;
+  float4 u = __ldcg(h), v = __ldcg(h + 1);
+  b.xmin = u.x; b.ymin = u.y; b.zmin = u.z; b.xmax = u.w; b.ymax = v.x; b.zmax = v.y;
+}
+__device__ inline RtBox union_box(const RtBox& l, const RtBox& r) {  // AABB(left,right), interval.cuh:83-88
+  RtBox o;
+  o.xmin = fminf(l.xmin, r.xmin); o.xmax = fmaxf(l.xmax, r.xmax);
+  o.ymin = fminf(l.ymin, r.ymin); o.ymax = fmaxf(l.ymax, r.ymax);
+  o.zmin = fminf(l.zmin, r.zmin); o.zmax = fmaxf(l.zmax, r.zmax);
+  return o;
+}
+
+// ---- fused bottom-up builder ------------------------------------------------------------------
+template <typename KeyT>
+__global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ perm,
+                                                       const float4* __restrict__ bv, const float4* __restrict__ tv,
+                                                       float4* __restrict__ sorted_tv, float4* nodes, int* flags, int n,
+                                                       int* root_out, float* root_box) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t p = perm[k];
+  const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
+  // gather the trace view into Morton order (leaf k <-> record k)
+  sorted_tv[3 * (size_t)k] = __ldg(tv + 3 * (size_t)p);
+  sorted_tv[3 * (size_t)k + 1] = __ldg(tv + 3 * (size_t)p + 1);
+  sorted_tv[3 * (size_t)k + 2] = __ldg(tv + 3 * (size_t)p + 2);
+  RtBox box = rt_prim_box(a, b, c);
+  uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
+  Delta<KeyT> D{keys, n};
+  int l = k, r = k;
+  while (true) {
+    if (l == 0 && r == n - 1) {  // root
+      *root_out = (int)ref;
+      root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+      return;
+    }
+    const int dl = D.adj(l - 1), dr = D.adj(r);
+    int s, side, mine;
+    if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
+    store_half(nodes, s, side, box, ref);
+    __threadfence();
+    const int other = atomicExch(flags + s, mine);
+    if (other == -1) return;  // sibling not there yet: it will finish this node
+    __threadfence();
+    RtBox sib;
+    load_half_box(nodes, s, side ^ 1, sib);
+    if (side == 0) { r = other; box = union_box(box, sib); } else { l = other; box = union_box(sib, box); }
+    ref = (uint32_t)s;
+  }
+}
+
+// ---- top-down Karras builder (reference numbering) --------------------------------------------
+template <typename KeyT>
+__global__ void __launch_bounds__(256) karras_topdown_kernel(const KeyT* __restrict__ keys, int n, float4* nodes, int* parent) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  Delta<KeyT> D{keys, n};
+  // determine_range_adapted, lbvh_builder.cu:103-182
+  const int dl = D.pair(i, i - 1), dr = D.pair(i, i + 1);
+  int d, dmin;
+  if (dr > dl) { d = 1; dmin = dl; } else { d = -1; dmin = dr; }
+  unsigned lmax = 1;
+  int nb = i + (int)lmax * d;
+  int cur = D.pair(i, nb);
+  while (cur > dmin) {
+    lmax <<= 1;
+    nb = i + (int)lmax * d;
+    if (nb < 0 || nb >= n) break;
+    cur = D.pair(i, nb);
+  }
+  unsigned len = 0;
+  for (unsigned t = lmax >> 1; t > 0; t >>= 1) {
+    int nbb = i + (int)(len + t) * d;
+    if (nbb >= 0 && nbb < n && D.pair(i, nbb) > dmin) len += t;
+  }
+  const int j = i + (int)len * d;
+  const int first = min(i, j), last = max(i, j);
+  // find_split_adapted, lbvh_builder.cu:186-221
+  int split = first;
+  if (first != last) {
+    const int common = D.pair(first, last);
+    int step = last - first;
+    do {
+      step = (step + 1) >> 1;
+      const int ns = split + step;
+      if (ns < last && D.pair(first, ns) > common) split = ns;
+    } while (step > 1);
+  }
+  // children, lbvh_builder.cu:264-286 (the delta re-checks there are always true)
+  const bool lleaf = split == first, rleaf = split + 1 == last;
+  // leaf references are completed (sphere bit, box) by the refit kernel; internal children get their slot now
+  float4* h = nodes + 4 * (size_t)i;
+  h[1].z = __uint_as_float(lleaf ? (RT_LEAF_BIT | (uint32_t)split) : (uint32_t)split);
+  h[3].z = __uint_as_float(rleaf ? (RT_LEAF_BIT | (uint32_t)(split + 1)) : (uint32_t)(split + 1));
+  // parent records: [0,n-1) internal nodes, [n-1, 2n-1) leaves; value = parent*2 + side
+  if (lleaf) parent[n - 1 + split] = 2 * i; else parent[split] = 2 * i;
+  if (rleaf) parent[n - 1 + split + 1] = 2 * i + 1; else parent[split + 1] = 2 * i + 1;
+  if (i == 0) parent[0] = -1;
+}
+
+__global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__ perm, const float4* __restrict__ bv,
+                                                   const float4* __restrict__ tv, float4* __restrict__ sorted_tv, float4* nodes,
+                                                   const int* __restrict__ parent, int* counters, int n, int* root_out, float* root_box) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t p = perm[k];
+  const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
+  sorted_tv[3 * (size_t)k] = __ldg(tv + 3 * (size_t)p);
+  sorted_tv[3 * (size_t)k + 1] = __ldg(tv + 3 * (size_t)p + 1);
+  sorted_tv[3 * (size_t)k + 2] = __ldg(tv + 3 * (size_t)p + 2);
+  RtBox box = rt_prim_box(a, b, c);
+  uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
+  if (n == 1) { *root_out = (int)ref; root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax; return; }
+  int pi = parent[n - 1 + k];
+  while (true) {  // set_aabb_kernel_adapted, lbvh_builder.cu:353-386, plus the missing fences (F9)
+    const int par = pi >> 1, side = pi & 1;
+    store_half(nodes, par, side, box, ref);
+    __threadfence();
+    if (atomicExch(counters + par, 1) == -1) return;  // counters were initialised to -1
+    __threadfence();
+    RtBox sib;
+    load_half_box(nodes, par, side ^ 1, sib);
+    box = side == 0 ? union_box(box, sib) : union_box(sib, box);
+    ref = (uint32_t)par;
+    pi = parent[par];
+    if (pi == -1) {
+      *root_out = 0;
+      root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+      return;
+    }
+  }
+}
+
+// ---- export in the reference's layouts --------------------------------------------------------
+struct RefNode44 {  // include/lbvh.cuh:6-28
+  float bbox[6]; uint32_t left, right, prim; uint16_t nleaf; uint16_t pad; uint32_t counter;
+};
+static_assert(sizeof(RefNode44) == 44, "LBVHNode layout");
+
+__global__ void karras_index_kernel(const float4* nodes, int n, int root, int* karras) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n - 1) return;
+  const uint32_t lr = __float_as_uint(nodes[4 * (size_t)s + 1].z), rr = __float_as_uint(nodes[4 * (size_t)s + 3].z);
+  if (!(lr & RT_LEAF_BIT)) karras[lr] = s;       // left child's index = split of the parent
+  if (!(rr & RT_LEAF_BIT)) karras[rr] = s + 1;   // right child's index = split + 1
+  if (s == root) karras[s] = 0;
+}
+__global__ void export_nodes_kernel(const float4* nodes, int n, int root, const int* karras, const float* root_box, RefNode44* out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n == 1) {
+    if (s == 0) { RefNode44 o; memset(&o, 0, sizeof(o)); for (int q = 0; q < 6; q++) o.bbox[q] = root_box[q]; o.nleaf = 1; out[0] = o; }
+    return;
+  }
+  if (s >= n - 1) return;
+  const int me = karras ? karras[s] : s;
+  uint32_t child_idx[2];
+  for (int side = 0; side < 2; side++) {
+    const float4 u = nodes[4 * (size_t)s + 2 * side], v = nodes[4 * (size_t)s + 2 * side + 1];
+    const uint32_t ref = __float_as_uint(v.z);
+    uint32_t idx;
+    RefNode44 o; memset(&o, 0, sizeof(o));
+    if (ref & RT_LEAF_BIT) { idx = (uint32_t)(n - 1) + (ref & RT_LEAF_MASK); o.prim = ref & RT_LEAF_MASK; o.nleaf = 1; }
+    else { idx = (uint32_t)(karras ? karras[ref] : (int)ref); }
+    child_idx[side] = idx;
+    float bb[6] = {u.x, u.w, u.y, v.x, u.z, v.y};  // xmin,xmax,ymin,ymax,zmin,zmax
+    if (ref & RT_LEAF_BIT) { for (int q = 0; q < 6; q++) o.bbox[q] = bb[q]; out[idx] = o; }
+    else { for (int q = 0; q < 6; q++) out[idx].bbox[q] = bb[q]; }
+  }
+  out[me].left = child_idx[0]; out[me].right = child_idx[1]; out[me].prim = 0; out[me].nleaf = 0; out[me].pad = 0; out[me].counter = 2;
+  if (s == root) for (int q = 0; q < 6; q++) out[me].bbox[q] = root_box[q];
+}
+__global__ void export_refs_kernel(const int2* refs, const uint32_t* perm, int n, int2* out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) out[k] = refs[perm[k]];
+}
+
+}  // namespace
+
+extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void* stream, float* ms_out) {
+  if (!s) { rt_set_error("rt_build_lbvh: null scene"); return RT_ERR_INVALID; }
+  if (morton_bits != 30 && morton_bits != 63) { rt_set_error("rt_build_lbvh: morton_bits must be 30 or 63"); return RT_ERR_INVALID; }
+  if (s->n == 0) { rt_set_error("rt_build_lbvh: scene has no primitives"); return RT_ERR_INVALID; }  // main.cu:44 guards N>0
+  RT_CUDA(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  uint32_t launches = 0;
+  if (ms_out) RT_CUDA(cudaEventRecord(s->ev0, st));
+  int rc = rt_build_codes_and_sort(s, morton_bits, flags, st, &launches);
+  if (rc) return rc;
+  const int n = s->n, grid = (n + 255) / 256;
+  int* root_dev = (int*)(s->bounds + 8);
+  float* root_box = s->bounds + 10;
+  if (flags & RT_BUILD_TOPDOWN) {
+    if (n > 1) {
+      if (morton_bits == 30) karras_topdown_kernel<uint32_t><<<(n - 1 + 255) / 256, 256, 0, st>>>(s->sorted_keys32, n, s->nodes, s->parent);
+      else karras_topdown_kernel<uint64_t><<<(n - 1 + 255) / 256, 256, 0, st>>>(s->sorted_keys64, n, s->nodes, s->parent);
+    }
+    refit_kernel<<<grid, 256, 0, st>>>(s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->parent, s->node_flags, n, root_dev, root_box);
+  } else {
+    if (morton_bits == 30)
+      bottom_up_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+    else
+      bottom_up_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+  }
+  RT_CUDA(cudaGetLastError());
+  s->built = true; s->built_bits = morton_bits; s->built_topdown = (flags & RT_BUILD_TOPDOWN) != 0;
+  s->root = INT32_MIN;  // fetched lazily (rt_scene_root) so that the build stays asynchronous
+  if (ms_out) {
+    RT_CUDA(cudaEventRecord(s->ev1, st));
+    RT_CUDA(cudaEventSynchronize(s->ev1));
+    RT_CUDA(cudaEventElapsedTime(ms_out, s->ev0, s->ev1));
+  }
+  return RT_OK;
+}
+
+extern "C" int rt_export_reference_layout(rt_scene* s, uint32_t* codes, uint64_t* codes64, void* refs8, void* nodes44, uint32_t* perm) {
+  if (!s) { rt_set_error("rt_export_reference_layout: null scene"); return RT_ERR_INVALID; }
+  if (!s->built) { rt_set_error("rt_export_reference_layout: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
+  RT_CUDA(cudaSetDevice(s->device));
+  RT_CUDA(cudaDeviceSynchronize());
+  const int n = s->n;
+  if (codes) {
+    if (!s->sorted_keys32) { rt_set_error("rt_export_reference_layout: built with 63-bit codes, pass codes64"); return RT_ERR_INVALID; }
+    RT_CUDA(cudaMemcpy(codes, s->sorted_keys32, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  }
+  if (codes64) {
+    if (!s->sorted_keys64) { rt_set_error("rt_export_reference_layout: built with 30-bit codes, pass codes"); return RT_ERR_INVALID; }
+    RT_CUDA(cudaMemcpy(codes64, s->sorted_keys64, (size_t)n * 8, cudaMemcpyDeviceToHost));
+  }
+  if (perm) RT_CUDA(cudaMemcpy(perm, s->sorted_perm, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  if (refs8) {
+    int2* tmp; RT_CUDA(cudaMalloc(&tmp, (size_t)n * 8));
+    export_refs_kernel<<<(n + 255) / 256, 256>>>(s->refs, s->sorted_perm, n, tmp);
+    cudaError_t e = cudaMemcpy(refs8, tmp, (size_t)n * 8, cudaMemcpyDeviceToHost);
+    cudaFree(tmp);
+    RT_CUDA(e);
+  }
+  if (nodes44) {
+    int root = 0;
+    RT_CUDA(cudaMemcpy(&root, s->bounds + 8, 4, cudaMemcpyDeviceToHost));
+    RefNode44* tmp; const size_t nn = (size_t)2 * n - 1;
+    RT_CUDA(cudaMalloc(&tmp, nn * sizeof(RefNode44)));
+    RT_CUDA(cudaMemset(tmp, 0, nn * sizeof(RefNode44)));
+    const int g = (n > 1 ? n - 1 + 255 : 256) / 256;
+    int* karras = nullptr;
+    if (!s->built_topdown && n > 1) { karras = s->node_karras; karras_index_kernel<<<g, 256>>>(s->nodes, n, root, karras); }
+    export_nodes_kernel<<<g, 256>>>(s->nodes, n, root, karras, s->bounds + 10, tmp);
+    cudaError_t e = cudaMemcpy(nodes44, tmp, nn * sizeof(RefNode44), cudaMemcpyDeviceToHost);
+    cudaFree(tmp);
+    RT_CUDA(e);
+  }
+  return RT_OK;
+}

@@ -1,0 +1,72 @@
+// rng.cuh — device XORWOW, bit-compatible with the cuRAND calls the reference makes:
+// curand_init (draw.cu:105,162), curand_uniform via randD (helper.cu:82-85), curand_normal via
+// standerdD (helper.cu:87-89).  Arithmetic follows curand_kernel.h / curand_uniform.h:69-72 /
+// curand_normal.h:70-87,313-326 (device branch: __sincosf, logf, sqrtf).  Built with -fmad=false:
+// x * 2^-32 + 2^-33 is a multiply and an add, as in the reference's parity build.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+struct Xorwow {
+  uint32_t v0, v1, v2, v3, v4, d;
+  uint32_t bm_flag;   // EXTRA_FLAG_NORMAL = 1 when a cached Box-Muller value is pending
+  float bm_extra;
+};
+
+__device__ __forceinline__ uint32_t xw_next(Xorwow& s) {
+  uint32_t t = (s.v0 ^ (s.v0 >> 2));
+  s.v0 = s.v1; s.v1 = s.v2; s.v2 = s.v3; s.v3 = s.v4;
+  s.v4 = (s.v4 ^ (s.v4 << 4)) ^ (t ^ (t << 1));
+  s.d += 362437u;
+  return s.v4 + s.d;
+}
+__device__ __forceinline__ float xw_uniform(Xorwow& s) {
+  uint32_t x = xw_next(s);
+  return x * 2.3283064e-10f + (2.3283064e-10f / 2.0f);
+}
+__device__ __forceinline__ float xw_normal(Xorwow& s) {
+  if (s.bm_flag != 1u) {
+    uint32_t x = xw_next(s), y = xw_next(s);
+    float u = x * 2.3283064e-10f + (2.3283064e-10f / 2);
+    float v = y * (2.3283064e-10f * 6.2831855f) + ((2.3283064e-10f * 6.2831855f) / 2);
+    float sq = sqrtf(-2.0f * logf(u));
+    float sn, cs;
+    __sincosf(v, &sn, &cs);
+    sn *= sq; cs *= sq;
+    s.bm_extra = cs; s.bm_flag = 1u;
+    return sn;
+  }
+  s.bm_flag = 0u;
+  return s.bm_extra;
+}
+// randD(start, end), helper.cu:82-85
+__device__ __forceinline__ float xw_rand(float a, float b, Xorwow& s) { float u = xw_uniform(s); return a + (b - a) * u; }
+
+// seed scramble of _curand_init_inplace (curand_kernel.h)
+__device__ __forceinline__ void xw_seed(uint64_t seed, uint32_t* v, uint32_t& d) {
+  uint32_t s0 = ((uint32_t)seed) ^ 0xaad26b49u;
+  uint32_t s1 = (uint32_t)(seed >> 32) ^ 0xf7dcefddu;
+  uint32_t t0 = 1099087573u * s0;
+  uint32_t t1 = 2591861531u * s1;
+  d = 6615241u + t1 + t0;
+  v[0] = 123456789u + t0; v[1] = 362436069u ^ t0; v[2] = 521288629u + t1; v[3] = 88675123u ^ t1; v[4] = 5783321u + t0;
+}
+
+// out = M * in over GF(2); M = 160 rows of 8 words (5 used), row b = image of basis vector b.
+// One subsequence skip of any length is ONE such product with a host-built power matrix
+// (rng_tables.cpp); all lanes of a warp normally share M, so the row loads are broadcasts.
+__device__ __forceinline__ void xw_matvec(const uint32_t* __restrict__ M, const uint32_t* in, uint32_t* out) {
+  uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    const uint32_t w = in[i];
+#pragma unroll 8
+    for (int j = 0; j < 32; j++) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(M + 8 * (i * 32 + j)));
+      const uint32_t b = __ldg(M + 8 * (i * 32 + j) + 4);
+      const uint32_t m = 0u - ((w >> j) & 1u);
+      r0 ^= a.x & m; r1 ^= a.y & m; r2 ^= a.z & m; r3 ^= a.w & m; r4 ^= b & m;
+    }
+  }
+  out[0] = r0; out[1] = r1; out[2] = r2; out[3] = r3; out[4] = r4;
+}

@@ -1,0 +1,249 @@
+// scene.cu — rt_scene_create / destroy / update: upload in the reference's SoA layout, repack on
+// the device into the arena layout described in common.cuh.
+// Replaces src/config_utils.cu:18-232 (≤17 cudaMalloc + pageable cudaMemcpy pairs and a leak of the
+// SoA component arrays, :205-209) by one arena and a handful of bulk copies.
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+static thread_local std::string g_err;
+void rt_set_error(const std::string& msg) { g_err = msg; }
+extern "C" const char* rt_last_error(void) { return g_err.c_str(); }
+extern "C" const char* rt_version(void) { return "b200rt 0.1 (sm_100a)"; }
+
+namespace {
+
+struct PackArgs {
+  const float *sc, *sr, *sm, *t0, *t1, *t2, *tn, *te1, *te2, *tm;
+  const int2* refs;
+  int n;
+};
+
+// one thread per file-order primitive: gather the reference SoA record, emit the three views
+__global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* mat, uint32_t* tri_prim, int* flags) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  int2 r = a.refs[i];
+  const float* m;
+  if (r.x == 0) {  // sphere
+    const float* c = a.sc + 3 * (size_t)r.y;
+    float rad = a.sr[r.y];
+    bv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
+    bv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    bv[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, RT_TAG_SPHERE);
+    tv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
+    tv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    tv[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    m = a.sm + 11 * (size_t)r.y;
+  } else {
+    size_t t = (size_t)r.y;
+    const float *p0 = a.t0 + 3 * t, *p1 = a.t1 + 3 * t, *p2 = a.t2 + 3 * t, *nn = a.tn + 3 * t, *e1 = a.te1 + 3 * t,
+                *e2 = a.te2 + 3 * t;
+    bv[3 * (size_t)i + 0] = make_float4(p0[0], p0[1], p0[2], p1[0]);
+    bv[3 * (size_t)i + 1] = make_float4(p1[1], p1[2], p2[0], p2[1]);
+    bv[3 * (size_t)i + 2] = make_float4(p2[2], 0.f, 0.f, RT_TAG_TRI);
+    tv[3 * (size_t)i + 0] = make_float4(p0[0], p0[1], p0[2], nn[0]);
+    tv[3 * (size_t)i + 1] = make_float4(nn[1], nn[2], e1[0], e1[1]);
+    tv[3 * (size_t)i + 2] = make_float4(e1[2], e2[0], e2[1], e2[2]);
+    tri_prim[t] = (uint32_t)i;
+    m = a.tm + 11 * t;
+  }
+  mat[3 * (size_t)i + 0] = make_float4(m[0], m[1], m[2], m[3]);
+  mat[3 * (size_t)i + 1] = make_float4(m[4], m[5], m[6], m[7]);
+  mat[3 * (size_t)i + 2] = make_float4(m[8], m[9], m[10], 0.f);
+  // scene-wide material flags drive the size of the wavefront continuation stack (render.cu).
+  // Same approximate-zero test as RGB::operator== (include/struct.cuh:20-23 via fequal, vec3.cuh:7-18).
+  bool shiny = !(fabsf(m[3]) < 1e-6f && fabsf(m[4]) < 1e-6f && fabsf(m[5]) < 1e-6f);
+  bool trans = !(fabsf(m[6]) < 1e-6f && fabsf(m[7]) < 1e-6f && fabsf(m[8]) < 1e-6f);
+  bool rough = m[10] > 0.0f;
+  int f = (shiny ? 1 : 0) | (trans ? 2 : 0) | (rough ? 4 : 0);
+  if (f) atomicOr(flags, f);
+}
+
+__global__ void pack_planes_kernel(const float* planes21, int np, PlaneRec* out, int* flags) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= np) return;
+  const float* p = planes21 + 21 * (size_t)i;
+  PlaneRec r;
+  for (int k = 0; k < 3; k++) { r.nor[k] = p[4 + k]; r.point[k] = p[7 + k]; }
+  for (int k = 0; k < 11; k++) r.mat[k] = p[10 + k];
+  r.pad = 0.f;
+  out[i] = r;
+  const float* m = r.mat;
+  bool shiny = !(fabsf(m[3]) < 1e-6f && fabsf(m[4]) < 1e-6f && fabsf(m[5]) < 1e-6f);
+  bool trans = !(fabsf(m[6]) < 1e-6f && fabsf(m[7]) < 1e-6f && fabsf(m[8]) < 1e-6f);
+  int f = (shiny ? 1 : 0) | (trans ? 2 : 0) | (m[10] > 0.0f ? 4 : 0);
+  if (f) atomicOr(flags, f);
+}
+
+// Triangle constructor on the device (include/object.cuh:177-191).  Compiled with -fmad=false and
+// IEEE div/sqrt, so results equal the g++-compiled host constructor bit for bit.
+__device__ inline float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ inline float3 sub3(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ inline float3 cross3(float3 a, float3 b) { return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ inline float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ inline bool fequal_dev(float a, float b) {
+  float diff = fabsf(a - b), largest = fmaxf(fabsf(a), fabsf(b));
+  if (largest < 1e-6f) return diff < 1e-6f;
+  return diff / largest < 1e-6f;
+}
+__device__ inline float3 normalize3(float3 a) {
+  float mag = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
+  if (fequal_dev(mag, 0.0f)) return f3(0.f, 0.f, 0.f);
+  float inv = 1.0f / mag;
+  return f3(a.x * inv, a.y * inv, a.z * inv);
+}
+__global__ void update_tris_kernel(int nt, const float* p0a, const float* p1a, const float* p2a, const uint32_t* tri_prim,
+                                   float4* bv, float4* tv) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nt) return;
+  float3 p0 = f3(p0a[3 * t], p0a[3 * t + 1], p0a[3 * t + 2]), p1 = f3(p1a[3 * t], p1a[3 * t + 1], p1a[3 * t + 2]),
+         p2 = f3(p2a[3 * t], p2a[3 * t + 1], p2a[3 * t + 2]);
+  float3 nor = normalize3(cross3(sub3(p1, p0), sub3(p2, p0)));
+  float3 a1 = cross3(sub3(p2, p0), nor), a2 = cross3(sub3(p1, p0), nor);
+  float s1 = 1.0f / dot3(a1, sub3(p1, p0)), s2 = 1.0f / dot3(a2, sub3(p2, p0));
+  float3 e1 = f3(a1.x * s1, a1.y * s1, a1.z * s1), e2 = f3(a2.x * s2, a2.y * s2, a2.z * s2);
+  size_t i = tri_prim[t];
+  bv[3 * i + 0] = make_float4(p0.x, p0.y, p0.z, p1.x);
+  bv[3 * i + 1] = make_float4(p1.y, p1.z, p2.x, p2.y);
+  bv[3 * i + 2] = make_float4(p2.z, 0.f, 0.f, RT_TAG_TRI);
+  tv[3 * i + 0] = make_float4(p0.x, p0.y, p0.z, nor.x);
+  tv[3 * i + 1] = make_float4(nor.y, nor.z, e1.x, e1.y);
+  tv[3 * i + 2] = make_float4(e1.z, e2.x, e2.y, e2.z);
+}
+
+size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct TempBuf {  // device staging copy of a caller array (host or device pointer)
+  void* p = nullptr;
+  cudaError_t load(const void* src, size_t bytes) {
+    if (bytes == 0) return cudaSuccess;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(p, src, bytes, cudaMemcpyDefault);
+  }
+  ~TempBuf() { if (p) cudaFree(p); }
+};
+
+}  // namespace
+
+extern "C" int rt_scene_num_prims(const rt_scene* s) { return s ? s->n : 0; }
+
+extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** out) {
+  if (!d || !out) { rt_set_error("rt_scene_create: null argument"); return RT_ERR_INVALID; }
+  *out = nullptr;
+  if (d->num_prims != d->num_spheres + d->num_triangles || d->num_prims < 0) {
+    rt_set_error("rt_scene_create: num_prims != num_spheres + num_triangles"); return RT_ERR_INVALID;
+  }
+  if ((unsigned)d->num_prims > RT_LEAF_MASK) { rt_set_error("rt_scene_create: more than 2^30-1 primitives"); return RT_ERR_INVALID; }
+  int ndev = 0;
+  RT_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) { rt_set_error("rt_scene_create: no such CUDA device"); return RT_ERR_CUDA; }
+  RT_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  RT_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {  // kernels are built for sm_100a only; there is no fallback path
+    rt_set_error(std::string("rt_scene_create: device is ") + prop.name + " (sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+                 "), this library is built for sm_100a only");
+    return RT_ERR_CUDA;
+  }
+  rt_scene* s = new rt_scene();
+  s->device = device; s->cfg = *d;
+  s->n = d->num_prims; s->ns = d->num_spheres; s->nt = d->num_triangles;
+  // null the borrowed pointers
+  s->cfg.sphere_c = s->cfg.sphere_r = s->cfg.sphere_mat = nullptr;
+  s->cfg.tri_p0 = s->cfg.tri_p1 = s->cfg.tri_p2 = s->cfg.tri_nor = s->cfg.tri_e1 = s->cfg.tri_e2 = s->cfg.tri_mat = nullptr;
+  s->cfg.refs = nullptr; s->cfg.suns = s->cfg.bulbs = s->cfg.planes = nullptr;
+  const size_t n = (size_t)s->n, n1 = n > 0 ? n : 1;
+  const size_t tiles_max = n1 / 2048 + 2;  // onesweep tiles are >= 2048 keys
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes ? bytes : 16); return o; };
+  size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 48), o_nodes = carve(n1 * 64);
+  size_t o_refs = carve(n1 * 8), o_tp = carve((size_t)(s->nt > 0 ? s->nt : 1) * 4);
+  size_t o_sun = carve((size_t)d->num_suns * sizeof(LightSun)), o_bulb = carve((size_t)d->num_bulbs * sizeof(LightBulb)),
+         o_pl = carve((size_t)d->num_planes * sizeof(PlaneRec));
+  size_t o_ka = carve(n1 * 8), o_kb = carve(n1 * 8), o_pa = carve(n1 * 4), o_pb = carve(n1 * 4);
+  size_t o_hist = carve(8 * 256 * 4), o_lb = carve(8 * tiles_max * 256 * 4), o_tk = carve(64 * 4);
+  size_t o_flags = carve(n1 * 4), o_par = carve(2 * n1 * 4), o_kar = carve(n1 * 4), o_bnd = carve(64);
+  s->arena_bytes = off;
+  cudaError_t e = cudaMalloc((void**)&s->arena, s->arena_bytes);
+  if (e != cudaSuccess) { rt_set_error(std::string("rt_scene_create: arena cudaMalloc: ") + cudaGetErrorString(e)); delete s; return RT_ERR_NOMEM; }
+  char* A = s->arena;
+  s->prim_bv = (float4*)(A + o_bv); s->prim_tv = (float4*)(A + o_tv); s->prim_mat = (float4*)(A + o_mat);
+  s->sorted_tv = (float4*)(A + o_stv); s->nodes = (float4*)(A + o_nodes); s->refs = (int2*)(A + o_refs);
+  s->tri_prim = (uint32_t*)(A + o_tp); s->suns = (LightSun*)(A + o_sun); s->bulbs = (LightBulb*)(A + o_bulb);
+  s->planes = (PlaneRec*)(A + o_pl); s->keys_a = (uint64_t*)(A + o_ka); s->keys_b = (uint64_t*)(A + o_kb);
+  s->perm_a = (uint32_t*)(A + o_pa); s->perm_b = (uint32_t*)(A + o_pb); s->hist = (uint32_t*)(A + o_hist);
+  s->lookback = (uint32_t*)(A + o_lb); s->tickets = (uint32_t*)(A + o_tk); s->node_flags = (int*)(A + o_flags);
+  s->parent = (int*)(A + o_par); s->node_karras = (int*)(A + o_kar); s->bounds = (float*)(A + o_bnd);
+  auto fail = [&](cudaError_t err, const char* what) {
+    rt_set_error(std::string("rt_scene_create: ") + what + ": " + cudaGetErrorString(err));
+    cudaFree(s->arena); delete s; return RT_ERR_CUDA;
+  };
+  {
+    TempBuf sc, sr, sm, t0, t1, t2, tn, te1, te2, tm, planes, flagbuf;
+    const size_t ns = (size_t)s->ns, nt = (size_t)s->nt;
+    if ((e = sc.load(d->sphere_c, ns * 12)) || (e = sr.load(d->sphere_r, ns * 4)) || (e = sm.load(d->sphere_mat, ns * 44)) ||
+        (e = t0.load(d->tri_p0, nt * 12)) || (e = t1.load(d->tri_p1, nt * 12)) || (e = t2.load(d->tri_p2, nt * 12)) ||
+        (e = tn.load(d->tri_nor, nt * 12)) || (e = te1.load(d->tri_e1, nt * 12)) || (e = te2.load(d->tri_e2, nt * 12)) ||
+        (e = tm.load(d->tri_mat, nt * 44)) || (e = planes.load(d->planes, (size_t)d->num_planes * 84)))
+      return fail(e, "upload");
+    if ((e = cudaMalloc(&flagbuf.p, 4)) || (e = cudaMemset(flagbuf.p, 0, 4))) return fail(e, "flags");
+    if (n && (e = cudaMemcpy(s->refs, d->refs, n * 8, cudaMemcpyDefault))) return fail(e, "refs");
+    if (d->num_suns && (e = cudaMemcpy(s->suns, d->suns, (size_t)d->num_suns * 24, cudaMemcpyDefault))) return fail(e, "suns");
+    if (d->num_bulbs && (e = cudaMemcpy(s->bulbs, d->bulbs, (size_t)d->num_bulbs * 24, cudaMemcpyDefault))) return fail(e, "bulbs");
+    if (n) {
+      PackArgs a{(const float*)sc.p, (const float*)sr.p, (const float*)sm.p, (const float*)t0.p, (const float*)t1.p,
+                 (const float*)t2.p, (const float*)tn.p, (const float*)te1.p, (const float*)te2.p, (const float*)tm.p, s->refs, s->n};
+      pack_prims_kernel<<<(unsigned)((n + 255) / 256), 256>>>(a, s->prim_bv, s->prim_tv, s->prim_mat, s->tri_prim, (int*)flagbuf.p);
+    }
+    if (d->num_planes) pack_planes_kernel<<<(d->num_planes + 63) / 64, 64>>>((const float*)planes.p, d->num_planes, s->planes, (int*)flagbuf.p);
+    if ((e = cudaGetLastError()) || (e = cudaDeviceSynchronize())) return fail(e, "pack kernels");
+    int f = 0;
+    if ((e = cudaMemcpy(&f, flagbuf.p, 4, cudaMemcpyDeviceToHost))) return fail(e, "flags readback");
+    s->any_shiny = f & 1; s->any_trans = f & 2; s->any_rough = f & 4;
+  }
+  if ((e = cudaEventCreate(&s->ev0)) || (e = cudaEventCreate(&s->ev1))) return fail(e, "events");
+  *out = s;
+  return RT_OK;
+}
+
+extern "C" int rt_scene_destroy(rt_scene* s) {
+  if (!s) return RT_OK;
+  cudaSetDevice(s->device);
+  rt_render_free_state(s);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  cudaFree(s->arena);
+  delete s;
+  return RT_OK;
+}
+
+extern "C" int rt_scene_update_triangles(rt_scene* s, const float* p0, const float* p1, const float* p2, void* stream) {
+  if (!s || !p0 || !p1 || !p2) { rt_set_error("rt_scene_update_triangles: null argument"); return RT_ERR_INVALID; }
+  if (s->nt == 0) return RT_OK;
+  RT_CUDA(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const float* src[3] = {p0, p1, p2};
+  const float* dev[3];
+  void* tmp[3] = {nullptr, nullptr, nullptr};
+  for (int k = 0; k < 3; k++) {
+    cudaPointerAttributes at;
+    cudaError_t e = cudaPointerGetAttributes(&at, src[k]);
+    if (e == cudaSuccess && at.type == cudaMemoryTypeDevice) { dev[k] = src[k]; continue; }
+    cudaGetLastError();
+    RT_CUDA(cudaMalloc(&tmp[k], (size_t)s->nt * 12));
+    RT_CUDA(cudaMemcpyAsync(tmp[k], src[k], (size_t)s->nt * 12, cudaMemcpyDefault, st));
+    dev[k] = (const float*)tmp[k];
+  }
+  update_tris_kernel<<<(s->nt + 255) / 256, 256, 0, st>>>(s->nt, dev[0], dev[1], dev[2], s->tri_prim, s->prim_bv, s->prim_tv);
+  RT_CUDA(cudaGetLastError());
+  s->built = false;
+  if (tmp[0] || tmp[1] || tmp[2]) {
+    RT_CUDA(cudaStreamSynchronize(st));
+    for (int k = 0; k < 3; k++) if (tmp[k]) cudaFree(tmp[k]);
+  }
+  return RT_OK;
+}

@@ -1,0 +1,159 @@
+/* include/rt_api.h — C ABI of the B200-native LBVH + ray-tracing core (libb200rt.so).
+ *
+ * Drop-in boundary for the two hot paths of GJ0407790/cuda_ray_tracer.  The reference has no
+ * FFI; its seam is four C++ host functions exchanging one POD struct of device pointers
+ * (SURVEY §8b).  Each entry point below names the reference interface it replaces (file:line in
+ * the reference tree).  Plain pointers and sizes only; every call returns 0 or a negative
+ * rt_status and never exits the process (the reference's CUDA_CHECK → exit(EXIT_FAILURE),
+ * main.cu:14-23, becomes a status + rt_last_error()).  There is no CPU fallback: every compute
+ * entry point fails with RT_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef RT_API_H
+#define RT_API_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  RT_OK = 0, RT_ERR_INVALID = -1, RT_ERR_CUDA = -2, RT_ERR_NOT_BUILT = -3, RT_ERR_IO = -4, RT_ERR_PARSE = -5,
+  RT_ERR_NOMEM = -6
+} rt_status;
+
+/* ---- scene description: the host-side content of StlConfig / RawConfig ----------------------
+ * replaces: initRawConfigFromStl + copyConfigDataToDevice (include/config_utils.cuh:11-16,
+ * src/config_utils.cu:18-199) and the RawConfig POD (include/config.hpp:75-126).
+ * Array layouts are the reference's: 12-byte vec3 (include/vec3.cuh:21-25), 44-byte Materials
+ * (include/object.cuh:17-38: color3, shininess3, trans3, ior, roughness), 8-byte
+ * PrimitiveReference {int32 type (0 sphere, 1 triangle), uint32 id_in_type_array}
+ * (include/object.cuh:72-88), Sun/Bulb 24 bytes (object.cuh:232-266), Plane 84 bytes
+ * (object.cuh:124-149: a,b,c,d, nor3, point3, Materials).  Pointers may be host or device
+ * memory (they are read with cudaMemcpyDefault), e.g. NCCL-broadcast device buffers. */
+typedef struct rt_scene_desc {
+  int32_t width, height;            /* png W H                      config.hpp:76-77  */
+  float   color[3];                 /* current colour               config.hpp:78     */
+  int32_t bounces, aa;              /*                              config.hpp:79-80  */
+  float   dof_focus, dof_lens;      /*                              config.hpp:81-82  */
+  float   forward[3], right[3], up[3], eye[3], target_up[3]; /*     config.hpp:84-88  */
+  float   expose;                   /* +INF = off                   config.hpp:90     */
+  int32_t fisheye, panorama;        /*                              config.hpp:91-92  */
+  float   ior, rough;               /*                              config.hpp:94-95  */
+  int32_t gi;                       /*                              config.hpp:96     */
+  float   trans[3], shine[3];       /*                              config.hpp:97-98  */
+  float   scene_min[3], scene_max[3]; /* RawConfig::scene_min/max_corner, config.hpp:112-113;
+                                         the reference leaves them at +INF/-INF */
+  int32_t num_spheres;   const float* sphere_c; const float* sphere_r; const float* sphere_mat;
+  int32_t num_triangles; const float* tri_p0; const float* tri_p1; const float* tri_p2;
+                         const float* tri_nor; const float* tri_e1; const float* tri_e2; const float* tri_mat;
+  int32_t num_prims;     const int32_t* refs;   /* file order, config.hpp:65 */
+  int32_t num_suns;      const float* suns;
+  int32_t num_bulbs;     const float* bulbs;
+  int32_t num_planes;    const float* planes;
+} rt_scene_desc;
+
+typedef struct rt_scene rt_scene;   /* opaque; owns one device arena on one GPU */
+
+/* replaces copyConfigDataToDevice / freeRawConfigDeviceMemory (config_utils.cuh:16,20) */
+int rt_scene_create(const rt_scene_desc* desc, int device, rt_scene** out);
+int rt_scene_destroy(rt_scene* scene);
+/* new vertex positions for every triangle (deforming scenes, "LBVH rebuilt every frame"):
+ * recomputes nor/e1/e2 on the device with the Triangle constructor's arithmetic
+ * (include/object.cuh:177-191).  Pointers host or device, [num_triangles][3] floats each. */
+int rt_scene_update_triangles(rt_scene* scene, const float* p0, const float* p1, const float* p2, void* stream);
+
+/* ---- LBVH build ------------------------------------------------------------------------------
+ * replaces build_lbvh_karas(RawConfig&, int morton_bits) (include/lbvh_builder.cuh:14,
+ * src/lbvh_builder.cu:401-521) and build_morton_codes_and_sort_primitives
+ * (include/lbvh_utils.cuh:22, src/lbvh_utils.cu:77-129).  morton_bits: 30 (the reference's
+ * hard-coded 10 bits/axis, lbvh_utils.cu:84) or 63 (21 bits/axis, not in the reference).
+ * Asynchronous on `stream` (a cudaStream_t, NULL = default stream) unless ms_out != NULL, in which
+ * case the call synchronises and returns the device time of the build in milliseconds. */
+enum {
+  RT_BOUNDS_FROM_DESC   = 0u,  /* use desc.scene_min/max verbatim: +INF/-INF reproduces the shipped
+                                  reference, where every Morton code is 0            */
+  RT_BOUNDS_COMPUTED    = 1u,  /* reduce the primitive AABBs on the device (what parse.cpp:147-155,
+                                  193-200 accumulates and drops)                                  */
+  RT_BUILD_TOPDOWN      = 2u   /* per-node Karras range/split search (lbvh_builder.cu:103-322) +
+                                  separate refit instead of the fused bottom-up builder           */
+};
+int rt_build_lbvh(rt_scene* scene, int morton_bits, unsigned flags, void* stream, float* ms_out);
+
+/* ---- render ----------------------------------------------------------------------------------
+ * replaces render(pixel_t* d_image, int w, int h, int aa, RawConfig* d_cfg) (include/draw.cuh:10,
+ * src/draw.cu:215-239) and everything below it (shootPrimaryRay, hitNearest, traverse_lbvh,
+ * diffuse/reflection/refraction/GI, checkPlane).  d_rgba: device RGBA8 [h][w] (pixel_t,
+ * include/libpng.h:23-27).  Optional outputs: d_hit_id int32 [h][w] = closest hit of sample 0's
+ * primary ray (file-order primitive index, -1 miss, -2-p plane p); d_written u8 [h][w] = 1 where
+ * a pixel was produced (F3: the reference's aa>=2 launch shape covers only part of the image
+ * when aa<32; uncovered pixels are left 0 here, uninitialised in the reference). */
+enum {
+  RT_SPP_REF          = 0u,   /* aa<=1: render_kernel; aa>=2: 32 samples/pixel over the reference's
+                                 launch shape (draw.cu:135-213,226-238)                 */
+  RT_SPP_TRUE         = 1u,   /* aa>=2: exactly aa samples for every pixel, seed (1234+pixel, s)   */
+  RT_TRAVERSE_REF_ORDER = 2u, /* left-first traversal, closest-hit shadow rays: the reference's exact
+                                 visiting order (bvh_traversal.cu:149-179) instead of near-first +
+                                 any-hit shadows                                                    */
+  RT_ROUGH_ZYX        = 4u,   /* draw order of the three unsequenced standerdD() arguments
+                                 (draw.cu:335-337): z,y,x instead of x,y,z                          */
+  RT_COUNTERS         = 8u    /* fill node/leaf counters (slower kernels)                          */
+};
+typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
+  int32_t tile_w, tile_h, num_ranks, rank;
+} rt_tile_set;
+typedef struct rt_counters {
+  uint64_t rays;            /* hitNearest calls with bounce != 0 (every BVH traversal)              */
+  uint64_t samples;         /* primary samples                                                      */
+  uint64_t nodes_visited;   /* 64-byte node fetches (RT_COUNTERS)                                   */
+  uint64_t leaf_tests;      /* primitive tests (RT_COUNTERS)                                        */
+  uint64_t shaded_hits;     /* hits whose material was fetched                                      */
+  uint32_t wavefront_iters, passes;
+  float    render_ms;       /* device time generate..resolve                                        */
+  uint32_t kernel_launches; /* kernels launched by this call                                        */
+  float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS)                    */
+} rt_counters;
+int rt_render(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
+              uint8_t* d_rgba, int32_t* d_hit_id, uint8_t* d_written, rt_counters* counters, void* stream);
+/* same, host buffers: device work + device->host copy of the image (main.cu:67-77) */
+int rt_render_host(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
+                   uint8_t* h_rgba, int32_t* h_hit_id, uint8_t* h_written, rt_counters* counters);
+/* closest hits for explicit rays (device arrays [n][3] origins and normalised directions):
+ * hitNearest for a bounce!=0 ray (draw.cu:292-318).  Outputs device int32[n] / float[n]. */
+int rt_trace(rt_scene* scene, int n, const float* d_org, const float* d_dir, unsigned flags,
+             int32_t* d_hit_id, float* d_hit_t, rt_counters* counters, void* stream);
+
+/* ---- parity dumps in the reference's exact layouts ---------------------------------------------
+ * codes: uint32[n] sorted d_morton_codes (config.hpp:109) (NULL ok); codes64: uint64[n] for
+ * morton_bits 63 (NULL ok); refs8: sorted PrimitiveReference[n]; nodes44: LBVHNode[2n-1]
+ * (include/lbvh.cuh:6-28; internal i in [0,n-2], leaf k at n-1+k; fields the reference leaves
+ * uninitialised are zero; visited_atomic_counter of internal nodes is 2); perm: uint32[n] sorted
+ * position -> file-order index.  All HOST pointers. */
+int rt_export_reference_layout(rt_scene* scene, uint32_t* codes, uint64_t* codes64, void* refs8,
+                               void* nodes44, uint32_t* perm);
+int rt_scene_num_prims(const rt_scene* scene);
+
+/* ---- host side of the drop-in surface --------------------------------------------------------- */
+typedef struct rt_host_scene rt_host_scene;
+/* replaces parseInput(char* argv[], StlConfig&) (include/parse.hpp:10, src/parse.cpp:16-222) */
+int  rt_parse_scene_file(const char* path, rt_host_scene** out);
+int  rt_host_scene_desc(const rt_host_scene* hs, rt_scene_desc* out);   /* borrows hs's arrays */
+const char* rt_host_scene_filename(const rt_host_scene* hs);             /* png W H <name>      */
+void rt_host_scene_bounds(const rt_host_scene* hs, float* mn3, float* mx3); /* parse.cpp:28 running bounds */
+void rt_host_scene_free(rt_host_scene* hs);
+/* Triangle constructor (include/object.cuh:177-191) on the host for n triangles */
+void rt_triangle_setup(int n, const float* p0, const float* p1, const float* p2, float* nor, float* e1, float* e2);
+/* replaces save_image(image_t*, const char*) (include/libpng.h:63, src/libpng.cpp:73-107): RGBA8,
+ * non-interlaced PNG written with zlib */
+int  rt_png_write(const char* path, int w, int h, const uint8_t* rgba);
+int  rt_png_read(const char* path, int* w, int* h, uint8_t** rgba_out);  /* load_image, libpng.h:53 */
+void rt_free(void* p);
+
+/* XORWOW state after curand_init(seed, subsequence, 0) (draw.cu:105,162): v0..v4, d.  Host. */
+void rt_xorwow_init(uint64_t seed, uint64_t subsequence, uint32_t* state6);
+
+const char* rt_last_error(void);
+const char* rt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
