@@ -1,0 +1,85 @@
+// main.cpp — `raytracer <scene.txt>`: the command-line entry of the reference (main.cu:25-94) on top
+// of the C ABI (include/rt_api.h).  Same positional argument, same stdout timing lines, same output
+// file (the name on the scene's `png W H name` line, written into the CWD).  Everything it computes
+// goes through libb200rt.so; there is no CPU rendering path.
+//
+// Extra flags (not in the reference):
+//   --bounds shipped|computed   Morton bounds: the reference as shipped (+INF/-INF, every code 0,
+//                               SURVEY F1) or the box parse.cpp accumulates and drops (default)
+//   --spp ref|true              aa>=2 sample semantics; default ref
+//   --ref-order                 left-first traversal + closest-hit shadow rays (reference visiting order)
+//   --bits 30|63                Morton code width
+//   --device N, --counters, --ids FILE (raw int32 hit ids), --repeat N
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "rt_api.h"
+
+static double now_s() { return std::chrono::duration<double>(std::chrono::high_resolution_clock::now().time_since_epoch()).count(); }
+static void die(const char* what) {  // CUDA_CHECK → exit(EXIT_FAILURE), main.cu:14-23
+  fprintf(stderr, "%s: %s\n", what, rt_last_error());
+  exit(EXIT_FAILURE);
+}
+
+int main(int argc, char* argv[]) {
+  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds shipped|computed] [--spp ref|true] [--ref-order] [--bits 30|63] [--device N] [--counters] [--ids FILE] [--repeat N]\n", argv[0]); return 1; }
+  unsigned bflags = RT_BOUNDS_COMPUTED, rflags = RT_SPP_REF;
+  int bits = 30, device = 0, repeat = 1; bool counters = false; std::string ids_path;
+  for (int i = 2; i < argc; i++) {
+    std::string a = argv[i];
+    if (a == "--bounds" && i + 1 < argc) bflags = strcmp(argv[++i], "shipped") == 0 ? RT_BOUNDS_FROM_DESC : RT_BOUNDS_COMPUTED;
+    else if (a == "--spp" && i + 1 < argc) { if (strcmp(argv[++i], "true") == 0) rflags |= RT_SPP_TRUE; }
+    else if (a == "--ref-order") rflags |= RT_TRAVERSE_REF_ORDER;
+    else if (a == "--bits" && i + 1 < argc) bits = atoi(argv[++i]);
+    else if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
+    else if (a == "--counters") { counters = true; rflags |= RT_COUNTERS; }
+    else if (a == "--ids" && i + 1 < argc) ids_path = argv[++i];
+    else if (a == "--repeat" && i + 1 < argc) repeat = atoi(argv[++i]);
+    else { fprintf(stderr, "unknown argument %s\n", argv[i]); return 1; }
+  }
+  rt_host_scene* hs = nullptr;
+  if (rt_parse_scene_file(argv[1], &hs) != RT_OK) { std::cout << rt_last_error() << std::endl; exit(1); }  // parse.cpp:22-25,218-221
+  rt_scene_desc d;
+  rt_host_scene_desc(hs, &d);
+
+  double t0 = now_s();
+  rt_scene* sc = nullptr;
+  if (rt_scene_create(&d, device, &sc) != RT_OK) die("rt_scene_create");
+  std::cout << "Initialize raw config time: " << now_s() - t0 << " seconds" << std::endl;  // main.cu:39
+
+  const size_t npx = (size_t)d.width * (size_t)d.height;
+  std::vector<uint8_t> img(npx * 4);
+  std::vector<int32_t> ids(ids_path.empty() ? 0 : npx);
+  rt_counters cnt; memset(&cnt, 0, sizeof(cnt));
+  for (int rep = 0; rep < repeat; rep++) {
+    if (d.num_prims > 0) {  // main.cu:44-46
+      float ms = 0.f;
+      if (rt_build_lbvh(sc, bits, bflags, nullptr, &ms) != RT_OK) die("rt_build_lbvh");
+      printf("LBVH Build time (N=%d): %.3f ms\n", d.num_prims, ms);  // lbvh_builder.cu:489
+    }
+    t0 = now_s();
+    if (rt_render_host(sc, d.width, d.height, d.aa, rflags, nullptr, img.data(), ids.empty() ? nullptr : ids.data(), nullptr, &cnt) != RT_OK)
+      die("rt_render");
+    const double wall = now_s() - t0;
+    std::cout << "Render time: " << cnt.render_ms * 1e-3 << " seconds" << std::endl;  // main.cu:71 (device time of render())
+    std::cout << "Transfer to host time: " << (wall - cnt.render_ms * 1e-3 > 0 ? wall - cnt.render_ms * 1e-3 : 0.0) << " seconds" << std::endl;  // main.cu:80
+    if (counters)
+      printf("[counters] rays=%llu samples=%llu nodes=%llu leaf_tests=%llu shaded=%llu iters=%u launches=%u Mrays/s=%.2f\n",
+             (unsigned long long)cnt.rays, (unsigned long long)cnt.samples, (unsigned long long)cnt.nodes_visited,
+             (unsigned long long)cnt.leaf_tests, (unsigned long long)cnt.shaded_hits, cnt.wavefront_iters, cnt.kernel_launches,
+             cnt.render_ms > 0 ? cnt.rays / (cnt.render_ms * 1e3) : 0.0);
+  }
+  if (rt_png_write(rt_host_scene_filename(hs), d.width, d.height, img.data()) != RT_OK)  // main.cu:82-83
+    fprintf(stderr, "%s\n", rt_last_error());  // save_image fails silently in the reference (libpng.cpp:73-107)
+  if (!ids_path.empty()) { FILE* f = fopen(ids_path.c_str(), "wb"); if (f) { fwrite(ids.data(), 4, npx, f); fclose(f); } }
+  t0 = now_s();
+  rt_scene_destroy(sc);
+  rt_host_scene_free(hs);
+  std::cout << "cudaFree time: " << now_s() - t0 << " seconds" << std::endl;  // main.cu:93
+  return 0;
+}
