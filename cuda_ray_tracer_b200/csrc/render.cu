@@ -1,12 +1,916 @@
-// render.cu — placeholder until the wavefront renderer lands (next commit).
+// render.cu — wavefront renderer: generate / traverse / shade / resolve, and rt_render / rt_trace.
+//
+// Replaces render(), render_kernel and render_kernel_warp_aa (src/draw.cu:94-239) and the recursive
+// shading below shootPrimaryRay (src/draw.cu:260-568).  The reference runs one thread per pixel (or
+// per sample) through a recursive call graph with a 64 KiB per-thread stack (main.cu:64).  Here every
+// sample is a small state machine with an explicit continuation stack in HBM: each wavefront
+// iteration traces exactly one ray per live sample (traverse.cuh, persistent warps over a compacted
+// queue) and then advances the sample to its next hitNearest call (shade_kernel), appending the new
+// ray to the next queue.  The state machine replays the reference's depth-first evaluation order, so
+// the per-sample XORWOW stream is consumed in the reference's order:
+//
+//   shade(hit H of ray R, weight W)            = shootPrimaryRay / the "if hit" bodies, draw.cu:269-282,
+//     diffuse(H)   * W(1-shin)(1-trans)          417-429, 507-518, 553-565
+//     reflect(R,H) * W shin            -> F_REFLECT frame
+//     refract(R,H) * W(1-shin)trans    -> F_REFRACT frame (for a reflection hit: of the OUTER ray/hit, draw.cu:424)
+//     gi(H)        * W(1-shin)(1-trans) color -> F_GI frame (primary and GI hits only)
+//
+// Colours are accumulated with the path weight pushed down ("throughput") instead of being returned up
+// the recursion; the products are the reference's, associated differently (image tolerance 1/255).
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
-int rt_render_free_state(rt_scene*) { return RT_OK; }
-extern "C" int rt_render(rt_scene*, int, int, int, unsigned, const rt_tile_set*, uint8_t*, int32_t*, uint8_t*, rt_counters*, void*) {
-  rt_set_error("rt_render: not implemented yet"); return RT_ERR_INVALID;
+#include "rng.cuh"
+#include "rng_tables.h"
+#include "rt_math.cuh"
+#include "traverse.cuh"
+
+namespace {
+
+// ---- per-render parameters (by value to every kernel) ------------------------------------------
+struct RenderParams {
+  RtCamera cam;
+  int W, H;
+  int mode;         // 0: aa==0 (exact pixel centre), 1: aa==1 (one jittered sample), 2: aa>=2 (one state per sample)
+  int spp;          // samples per pixel actually traced
+  int covered;      // pixels [0,covered) are rendered
+  int tile_w, tile_h, tiles_x, num_ranks, rank, slots_per_tile;
+  int slot0, npix, S;   // this pass: pixel slots [slot0, slot0+npix), S = npix * spp samples
+  int depth;        // continuation stack depth (frames per sample)
+  int ref_order, rough_zyx, need_rng;
+  int num_lights;
+};
+
+struct RenderBuffers {
+  uint4 *rng0, *rng1;     // XORWOW v0..v3 | v4, d, box-muller flag, cached normal
+  float4* accum;          // linear rgba per sample
+  uint32_t* ctl;          // stack pointer per sample
+  float4* frames;         // [(level*4 + q) * S + sample]
+  float4 *qa, *qb;        // ray queues, 2 float4 per ray
+  float2* hits;           // per queue slot
+  uint32_t* counters;     // [0] fetch ticket, [1] out-queue length, [2] overflow flag
+  unsigned long long* stats;  // [0] nodes, [1] leaf tests, [2] shaded hits
+  const uint32_t* rng_mats;   // power matrices P^m
+  const uint32_t* rng_base;   // base vectors for mode 0/1
+};
+
+enum : unsigned {
+  T_W_PRIMARY = 1, T_W_GI, T_W_REFLECT, T_W_REFRACT1, T_W_REFRACT2,  // a ray is in flight; resumed with its hit
+  T_DIFFUSE,                                                           // shadow ray of light `li` in flight
+  T_REFLECT, T_REFRACT, T_GI                                           // pending calls
+};
+
+__device__ __forceinline__ unsigned hdr_pack(unsigned type, int bounce, unsigned flag) {
+  return type | (((unsigned)bounce & 0xFFFFu) << 8) | (flag << 24);
 }
-extern "C" int rt_render_host(rt_scene*, int, int, int, unsigned, const rt_tile_set*, uint8_t*, int32_t*, uint8_t*, rt_counters*) {
-  rt_set_error("rt_render_host: not implemented yet"); return RT_ERR_INVALID;
+__device__ __forceinline__ int hdr_bounce(unsigned h) { return (int)(short)((h >> 8) & 0xFFFFu); }
+
+// pixel slot -> pixel.  Slots enumerate the rank's tiles (tile t belongs to rank t % num_ranks), row-major
+// inside a tile; slots that fall outside the image (edge tiles) are dead.
+__device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, int slot, int& x, int& y, int& pix) {
+  const int lt = slot / P.slots_per_tile, r = slot - lt * P.slots_per_tile;
+  const int t = lt * P.num_ranks + P.rank;
+  const int tx = t % P.tiles_x, ty = t / P.tiles_x;
+  x = tx * P.tile_w + r % P.tile_w;
+  y = ty * P.tile_h + r / P.tile_w;
+  pix = y * P.W + x;
+  return x < P.W && y < P.H && pix < P.covered;
 }
-extern "C" int rt_trace(rt_scene*, int, const float*, const float*, unsigned, int32_t*, float*, rt_counters*, void*) {
-  rt_set_error("rt_trace: not implemented yet"); return RT_ERR_INVALID;
+__device__ __forceinline__ bool pixel_to_slot(const RenderParams& P, int pix, int& slot) {
+  const int x = pix % P.W, y = pix / P.W;
+  const int tx = x / P.tile_w, ty = y / P.tile_h;
+  const int t = ty * P.tiles_x + tx;
+  if (t % P.num_ranks != P.rank) return false;
+  slot = (t / P.num_ranks) * P.slots_per_tile + (y - ty * P.tile_h) * P.tile_w + (x - tx * P.tile_w);
+  return true;
+}
+
+__device__ __forceinline__ void rng_load(const RenderBuffers& B, int i, Xorwow& r) {
+  const uint4 a = B.rng0[i], b = B.rng1[i];
+  r.v0 = a.x; r.v1 = a.y; r.v2 = a.z; r.v3 = a.w; r.v4 = b.x; r.d = b.y; r.bm_flag = b.z; r.bm_extra = __uint_as_float(b.w);
+}
+__device__ __forceinline__ void rng_store(const RenderBuffers& B, int i, const Xorwow& r) {
+  B.rng0[i] = make_uint4(r.v0, r.v1, r.v2, r.v3);
+  B.rng1[i] = make_uint4(r.v4, r.d, r.bm_flag, __float_as_uint(r.bm_extra));
+}
+
+// warp-aggregated append of one ray per participating lane (called with the whole warp converged)
+__device__ __forceinline__ void queue_append(float4* __restrict__ q, uint32_t* count, bool has, V3 o, V3 d, float tlimit, unsigned tag) {
+  const unsigned m = __ballot_sync(0xffffffffu, has);
+  if (m == 0u) return;
+  const unsigned lane = threadIdx.x & 31;
+  unsigned base = 0;
+  if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(count, (unsigned)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+  if (has) {
+    const size_t r = (size_t)base + __popc(m & ((1u << lane) - 1u));
+    q[2 * r] = make_float4(o.x, o.y, o.z, tlimit);
+    q[2 * r + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(tag));
+  }
+}
+
+// ---- RNG seeding -------------------------------------------------------------------------------
+// mode 0/1: curand_init(1234, pixel, 0) (draw.cu:105).  Thread g handles pixel h*256 + m with m uniform
+// across the warp, so the 160 matrix rows are broadcast loads (rng.cuh).
+__global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams P, const RenderBuffers B, int hn) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = g / hn, h = g - m * hn;
+  if (m >= 256) return;
+  const int pix = h * 256 + m;
+  if (pix >= P.covered) return;
+  int slot;
+  if (!pixel_to_slot(P, pix, slot)) return;
+  if (slot < P.slot0 || slot >= P.slot0 + P.npix) return;
+  uint32_t in[5], out[5];
+  const uint32_t* bv = B.rng_base + 8 * (size_t)h;
+#pragma unroll
+  for (int k = 0; k < 5; k++) in[k] = __ldg(bv + k);
+  if (m) xw_matvec(B.rng_mats + (size_t)m * RT_RNG_MATRIX_WORDS, in, out);
+  else { for (int k = 0; k < 5; k++) out[k] = in[k]; }
+  uint32_t v[5], d; xw_seed(1234ull, v, d);
+  Xorwow r; r.v0 = out[0]; r.v1 = out[1]; r.v2 = out[2]; r.v3 = out[3]; r.v4 = out[4]; r.d = d; r.bm_flag = 0u; r.bm_extra = 0.f;
+  rng_store(B, slot - P.slot0, r);
+}
+
+// ---- generate: RNG state, pixel jitter, primary ray (Ray::Ray(x,y,state,cfg), src/struct.cu:16-62) ---
+__global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool live = i < P.S;
+  int s = 0, lp = 0, x = 0, y = 0, pix = 0;
+  if (live) {
+    s = i / P.npix; lp = i - s * P.npix;
+    live = slot_to_pixel(P, P.slot0 + lp, x, y, pix);
+  }
+  bool has = false; V3 eye = mk3(0, 0, 0), dir = mk3(0, 0, 0);
+  if (i < P.S) {
+    B.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.ctl[i] = 0u;
+  }
+  if (live) {
+    Xorwow rng; rng.v0 = rng.v1 = rng.v2 = rng.v3 = rng.v4 = rng.d = 0u; rng.bm_flag = 0u; rng.bm_extra = 0.f;
+    bool rng_dirty = false;
+    float fx = (float)x, fy = (float)y;
+    if (P.mode == 2) {  // curand_init(1234 + pixel_idx, lane_id, 0), draw.cu:162
+      uint32_t v[5], d, out[5];
+      xw_seed(1234ull + (unsigned long long)pix, v, d);
+      if (s) xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);
+      else { for (int k = 0; k < 5; k++) out[k] = v[k]; }
+      rng.v0 = out[0]; rng.v1 = out[1]; rng.v2 = out[2]; rng.v3 = out[3]; rng.v4 = out[4]; rng.d = d;
+      const float jx = xw_rand(-0.5f, 0.5f, rng);  // draw.cu:165-169
+      const float jy = xw_rand(-0.5f, 0.5f, rng);
+      fx = (float)x + jx; fy = (float)y + jy;
+      rng_dirty = true;
+    } else if (P.need_rng) {
+      rng_load(B, i, rng);
+      if (P.mode == 1) {  // draw.cu:118-123
+        fx = x + xw_rand(-0.5f, 0.5f, rng);
+        fy = y + xw_rand(-0.5f, 0.5f, rng);
+        rng_dirty = true;
+      }
+    }
+    // struct.cu:16-62
+    const RtCamera& C = P.cam;
+    const V3 fwd = mk3(C.forward[0], C.forward[1], C.forward[2]), right = mk3(C.right[0], C.right[1], C.right[2]),
+             up = mk3(C.up[0], C.up[1], C.up[2]), ceye = mk3(C.eye[0], C.eye[1], C.eye[2]);
+    const float max_dim = fmax((float)C.width, (float)C.height);
+    float sx = (2.0f * fx - C.width) / max_dim;
+    float sy = (C.height - 2.0f * fy) / max_dim;
+    eye = ceye;
+    if (C.fisheye) {
+      dir = (sx * right + sy * up) + sqrt(1.0f - pow(sx, 2) - pow(sy, 2)) * fwd;
+    } else if (C.panorama) {
+      sx = (float)fx / (float)C.width;
+      sy = (float)fy / (float)C.height;
+      const float theta = (sx - 0.5f) * 2.0f * 3.14159265358979323846f;
+      const float phi = (sy - 0.5f) * 3.14159265358979323846f;
+      dir = cos(phi) * (cos(theta) * fwd + sin(theta) * right) - sin(phi) * up;
+      dir = normalize3(dir);
+    } else if (C.dof_focus != 0.0f) {
+      const float theta = xw_rand(0.0f, 2.0f * 3.14159265358979323846f, rng);
+      const float r = xw_rand(0.0f, C.dof_lens, rng);
+      rng_dirty = true;
+      const float lx = r * cos(theta);
+      const float ly = r * sin(theta);
+      eye = eye + lx * up + ly * right;
+      const V3 old_dir = fwd + sx * right + sy * up;
+      dir = (ceye + normalize3(old_dir) * C.dof_focus - eye) / C.dof_focus;
+    } else {
+      dir = fwd + sx * right + sy * up;
+    }
+    dir = normalize3(dir);
+    if (rng_dirty) rng_store(B, i, rng);
+    if (C.bounces != 0) {  // hitNearest: a ray with bounce == 0 hits nothing (draw.cu:294)
+      has = true;
+      B.frames[(size_t)i] = make_float4(__uint_as_float(hdr_pack(T_W_PRIMARY, C.bounces, 0u)), 1.f, 1.f, 1.f);
+      B.ctl[i] = 1u;
+    } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
+  }
+  queue_append(qout, B.counters + 1, has, eye, dir, INFINITY, (unsigned)i);
+}
+
+// ---- shade -------------------------------------------------------------------------------------
+struct SurfHit { V3 point, normal, color, shin, trans; float ior, rough; int file_id; };
+
+__device__ __forceinline__ void load_material(const float4* __restrict__ m, SurfHit& h) {
+  const float4 a = __ldg(m), b = __ldg(m + 1), c = __ldg(m + 2);
+  h.color = mk3(a.x, a.y, a.z); h.shin = mk3(a.w, b.x, b.y); h.trans = mk3(b.z, b.w, c.x); h.ior = c.y; h.rough = c.z;
+}
+// rebuild the ObjectInfo the reference's intersection routines return (point, facing normal, material)
+__device__ __forceinline__ void reconstruct_hit(const RtDeviceScene& sc, int id, float t, V3 o, V3 d, SurfHit& h) {
+  h.point = t * d + o;
+  if (id >= 0) {
+    const unsigned k = (unsigned)id & RT_LEAF_MASK;
+    const float4 a = __ldg(sc.sorted_tv + 3 * (size_t)k);
+    if ((unsigned)id & RT_SPHERE_BIT) {  // struct.cu:76-108
+      const V3 c = mk3(a.x, a.y, a.z);
+      const V3 cr0 = c - o;
+      const bool inside = dot(cr0, cr0) < a.w * a.w;
+      h.normal = normalize3(inside ? (c - h.point) : (h.point - c));
+    } else {  // struct.cu:124,160
+      const float4 b = __ldg(sc.sorted_tv + 3 * (size_t)k + 1);
+      const V3 nor = mk3(a.w, b.x, b.y);
+      h.normal = (dot(d, nor) < 0.0f) ? nor : -nor;
+    }
+    h.file_id = (int)__ldg(sc.perm + k);
+    load_material(sc.prim_mat + 3 * (size_t)h.file_id, h);
+  } else {  // plane -2-p, draw.cu:597-611
+    const int p = -2 - id;
+    const float* pl = reinterpret_cast<const float*>(sc.planes + p);
+    const V3 nor = mk3(__ldg(pl), __ldg(pl + 1), __ldg(pl + 2));
+    h.normal = (dot(nor, d) < 0.0f) ? nor : -nor;
+    h.color = mk3(__ldg(pl + 6), __ldg(pl + 7), __ldg(pl + 8)); h.shin = mk3(__ldg(pl + 9), __ldg(pl + 10), __ldg(pl + 11));
+    h.trans = mk3(__ldg(pl + 12), __ldg(pl + 13), __ldg(pl + 14)); h.ior = __ldg(pl + 15); h.rough = __ldg(pl + 16);
+    h.file_id = id;
+  }
+}
+
+// setExpose, helper.cu:40-45: the subtraction is done in double
+__device__ __forceinline__ float set_expose(float c, float expose) { return expose == float(INFINITY) ? c : 1.0 - exp(-expose * c); }
+
+// vec3(standerdD, standerdD, standerdD), draw.cu:335-337,395-397: the three draws are unsequenced
+// constructor arguments; zyx selects right-to-left evaluation
+__device__ __forceinline__ V3 rough_offset(float rough, Xorwow& rng, int zyx) {
+  float a, b, c;
+  if (zyx) { c = xw_normal(rng) * rough; b = xw_normal(rng) * rough; a = xw_normal(rng) * rough; }
+  else { a = xw_normal(rng) * rough; b = xw_normal(rng) * rough; c = xw_normal(rng) * rough; }
+  return mk3(a, b, c);
+}
+
+__global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
+                                                   const float4* __restrict__ qin, const unsigned n_in, float4* __restrict__ qout,
+                                                   int32_t* __restrict__ hit_id_out) {
+  const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+  bool emit = false, shaded = false; V3 eo = mk3(0, 0, 0), ed = mk3(0, 0, 0); float elimit = INFINITY; unsigned etag = 0u;
+  if (r < n_in) {
+    const float4 q0 = __ldcs(qin + 2 * (size_t)r), q1 = __ldcs(qin + 2 * (size_t)r + 1);
+    const float2 hv = __ldcs(B.hits + r);
+    const V3 o = mk3(q0.x, q0.y, q0.z), d = mk3(q1.x, q1.y, q1.z);
+    const int i = (int)(__float_as_uint(q1.w) & ~RT_RAY_ANYHIT);
+    const float ht = hv.x; const int hid = __float_as_int(hv.y);
+    const size_t S = (size_t)P.S;
+    float4* const F = B.frames + i;  // frame slot (L,q) is F[(L*4+q)*S]
+    int sp = (int)B.ctl[i];
+    Xorwow rng; bool rng_loaded = false, rng_dirty = false;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); bool acc_loaded = false, acc_dirty = false;
+    bool overflow = false;
+    const int nsuns = sc.num_suns, nlights = sc.num_suns + sc.num_bulbs;
+    const float expose = P.cam.expose;
+
+#define FR(L, q) F[(size_t)((L) * 4 + (q)) * S]
+#define NEED_RNG() do { if (!rng_loaded) { rng_load(B, i, rng); rng_loaded = true; } rng_dirty = true; } while (0)
+#define NEED_ACC() do { if (!acc_loaded) { acc = B.accum[i]; acc_loaded = true; } acc_dirty = true; } while (0)
+
+    // state of the diffuse light loop (draw.cu:342-374)
+    bool in_diffuse = false; int li = 0;
+    V3 df_point = mk3(0, 0, 0), df_origin = mk3(0, 0, 0), df_nrm = mk3(0, 0, 0), df_color = mk3(0, 0, 0), df_w = mk3(0, 0, 0);
+    bool df_frame_valid = false;  // frame slots q1..q3 already hold this diffuse state
+
+    // ---- 1. resume the frame whose ray has just been traced ----
+    sp--;
+    const float4 f0 = FR(sp, 0);
+    const unsigned hdr = __float_as_uint(f0.x);
+    const unsigned type = hdr & 0xFFu;
+    const int b = hdr_bounce(hdr);  // bounce of the traced ray
+    const V3 Wt = mk3(f0.y, f0.z, f0.w);
+
+    if (type == T_DIFFUSE) {
+      const float4 f1 = FR(sp, 1), f2 = FR(sp, 2), f3 = FR(sp, 3);
+      li = (int)(hdr >> 8);
+      df_point = mk3(f0.y, f0.z, f0.w); df_origin = mk3(f1.x, f1.y, f1.z); df_nrm = mk3(f1.w, f2.x, f2.y);
+      df_color = mk3(f2.z, f2.w, f3.x); df_w = mk3(f3.y, f3.z, f3.w);
+      in_diffuse = true; df_frame_valid = true;
+      // shadow test result, draw.cu:350-353 (sun: any hit) / :365-368 (bulb: hit closer than the bulb)
+      V3 ldir; float lt = 0.f; V3 lcol;
+      bool occluded;
+      if (li < nsuns) {
+        const LightSun& L = sc.suns[li];
+        ldir = mk3(L.dir[0], L.dir[1], L.dir[2]); lcol = mk3(L.color[0], L.color[1], L.color[2]);
+        occluded = hid != -1;
+      } else {
+        const LightBulb& L = sc.bulbs[li - nsuns];
+        ldir = mk3(L.point[0], L.point[1], L.point[2]) - df_point; lcol = mk3(L.color[0], L.color[1], L.color[2]);
+        lt = length3(ldir);
+        occluded = hid != -1 && ht < lt;
+      }
+      if (!occluded) {
+        const float lambert = fmax(dot(df_nrm, normalize3(ldir)), 0.0f);
+        const float cr = df_color.x * (lcol.x * lambert), cg = df_color.y * (lcol.y * lambert), cb = df_color.z * (lcol.z * lambert);
+        float er = set_expose(cr, expose), eg = set_expose(cg, expose), eb = set_expose(cb, expose);
+        if (li >= nsuns) {  // getColorBulb, draw.cu:649-659
+          const float fall = 1.0f / pow(lt, 2);
+          er = er * fall; eg = eg * fall; eb = eb * fall;
+        }
+        NEED_ACC();
+        acc.x += df_w.x * er; acc.y += df_w.y * eg; acc.z += df_w.z * eb;
+      }
+      li++;
+    } else if (type == T_W_REFRACT1) {
+      // refractionLight after the inside ray, draw.cu:484-495 (a miss leaves the default ObjectInfo)
+      V3 normal = mk3(0.f, 0.f, 0.f), ip = mk3(0.f, 0.f, 0.f); float ior = 1.458f;
+      if (hid != -1) {
+        SurfHit oh; reconstruct_hit(sc, hid, ht, o, d, oh);
+        normal = normalize3(oh.normal); ior = oh.ior; ip = oh.point;
+      }
+      const float k = 1.0f - ior * ior * (1.0f - pow(dot(normal, d), 2));
+      const V3 rdir = ior * d - (ior * (dot(normal, d)) + sqrt(k)) * normal;
+      const int nb = b - 1;
+      if (nb != 0) {
+        FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_W_REFRACT2, nb, 0u)), Wt.x, Wt.y, Wt.z); sp++;
+        emit = true; eo = ip - normal * 0.0001f; ed = normalize3(rdir); elimit = INFINITY; etag = (unsigned)i;
+      }
+    } else {
+      // T_W_PRIMARY / T_W_GI / T_W_REFLECT / T_W_REFRACT2: the "if hit" body
+      const unsigned flag = hdr >> 24;
+      if (type == T_W_PRIMARY && hit_id_out) {
+        const int s = i / P.npix;
+        if (s == 0) {
+          int x, y, pix; slot_to_pixel(P, P.slot0 + (i - s * P.npix), x, y, pix);
+          int out_id = hid;
+          if (hid >= 0) out_id = (int)__ldg(sc.perm + ((unsigned)hid & RT_LEAF_MASK));
+          hit_id_out[pix] = out_id;
+        }
+      }
+      if (hid == -1) {
+        if (type == T_W_REFLECT && flag) sp--;  // the provisional refract(outer) frame is never evaluated
+      } else {
+        SurfHit h; reconstruct_hit(sc, hid, ht, o, d, h);
+        if (type == T_W_PRIMARY) { NEED_ACC(); acc.w = 1.0f; }  // color.a = 1, draw.cu:281
+        const V3 one = mk3(1.0f, 1.0f, 1.0f);
+        const V3 ms = one - h.shin;
+        const V3 w_diff = mul3(Wt, mul3(ms, one - h.trans));
+        const V3 w_refl = mul3(Wt, h.shin);
+        const V3 w_refr = mul3(Wt, mul3(ms, h.trans));
+        const bool shiny = !rgb_is_zero(h.shin), transp = !rgb_is_zero(h.trans);
+        // frames are pushed in reverse evaluation order: gi, refract, reflect, then diffuse runs now
+        if ((type == T_W_PRIMARY || type == T_W_GI) && P.cam.gi != 0) {
+          const int g = type == T_W_PRIMARY ? P.cam.gi : b;
+          if (sp < P.depth) {
+            const V3 wg = mul3(w_diff, h.color);
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_GI, g, 0u)), wg.x, wg.y, wg.z);
+            FR(sp, 1) = make_float4(h.point.x, h.point.y, h.point.z, h.normal.x);
+            FR(sp, 2) = make_float4(h.normal.y, h.normal.z, 0.f, 0.f);
+            sp++;
+          } else overflow = true;
+        }
+        if (type == T_W_REFLECT) {
+          if (flag) { const float4 t0 = FR(sp - 1, 0); FR(sp - 1, 0) = make_float4(t0.x, w_refr.x, w_refr.y, w_refr.z); }
+        } else if (transp && b > 0) {
+          if (sp < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_REFRACT, b, 0u)), w_refr.x, w_refr.y, w_refr.z);
+            FR(sp, 1) = make_float4(d.x, d.y, d.z, h.point.x);
+            FR(sp, 2) = make_float4(h.point.y, h.point.z, h.normal.x, h.normal.y);
+            FR(sp, 3) = make_float4(h.normal.z, h.ior, 0.f, 0.f);
+            sp++;
+          } else overflow = true;
+        }
+        if (shiny && b > 0) {
+          if (sp < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_REFLECT, b, transp ? 1u : 0u)), w_refl.x, w_refl.y, w_refl.z);
+            FR(sp, 1) = make_float4(d.x, d.y, d.z, h.point.x);
+            FR(sp, 2) = make_float4(h.point.y, h.point.z, h.normal.x, h.normal.y);
+            FR(sp, 3) = make_float4(h.normal.z, h.ior, h.rough, 0.f);
+            sp++;
+          } else overflow = true;
+        }
+        // diffuseLight, draw.cu:329-377
+        shaded = true;
+        V3 nrm = h.normal;
+        if (h.rough > 0.0f) { NEED_RNG(); nrm = nrm + rough_offset(h.rough, rng, P.rough_zyx); }
+        df_nrm = normalize3(nrm);
+        df_point = h.point; df_origin = h.point + h.normal * 0.001f; df_color = h.color; df_w = w_diff;
+        in_diffuse = true; li = 0; df_frame_valid = false;
+      }
+    }
+
+    // ---- 2. run until a ray is emitted or the stack is empty ----
+    while (!emit) {
+      if (in_diffuse) {
+        if (li < nlights) {
+          V3 ldir; float lim = INFINITY;
+          if (li < nsuns) { const LightSun& L = sc.suns[li]; ldir = mk3(L.dir[0], L.dir[1], L.dir[2]); }
+          else {
+            const LightBulb& L = sc.bulbs[li - nsuns];
+            ldir = mk3(L.point[0], L.point[1], L.point[2]) - df_point;
+            lim = length3(ldir);
+          }
+          if (sp < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(T_DIFFUSE | ((unsigned)li << 8)), df_point.x, df_point.y, df_point.z);
+            if (!df_frame_valid) {
+              FR(sp, 1) = make_float4(df_origin.x, df_origin.y, df_origin.z, df_nrm.x);
+              FR(sp, 2) = make_float4(df_nrm.y, df_nrm.z, df_color.x, df_color.y);
+              FR(sp, 3) = make_float4(df_color.z, df_w.x, df_w.y, df_w.z);
+            }
+            sp++;
+            emit = true; eo = df_origin; ed = normalize3(ldir);  // Ray(eye, dir, 1) normalises, object.cuh:69
+            elimit = lim; etag = (unsigned)i | RT_RAY_ANYHIT;
+            break;
+          }
+          overflow = true; li = nlights;
+        }
+        in_diffuse = false;
+        continue;
+      }
+      if (sp == 0) break;  // sample finished
+      sp--;
+      const float4 g0 = FR(sp, 0);
+      const unsigned gh = __float_as_uint(g0.x);
+      const unsigned gt = gh & 0xFFu;
+      const int gb = hdr_bounce(gh);
+      const V3 W = mk3(g0.y, g0.z, g0.w);
+      if (gt == T_REFLECT) {  // reflectionLight, draw.cu:389-437
+        const float4 g1 = FR(sp, 1), g2 = FR(sp, 2), g3 = FR(sp, 3);
+        const V3 rd = mk3(g1.x, g1.y, g1.z), hp = mk3(g1.w, g2.x, g2.y), hn = mk3(g2.z, g2.w, g3.x);
+        const float hior = g3.y, hrough = g3.z;
+        const bool transp = (gh >> 24) != 0u;
+        V3 normal = hn;
+        if (hrough > 0.0f) { NEED_RNG(); normal = normal + rough_offset(hrough, rng, P.rough_zyx); }
+        normal = normalize3(normal);
+        const V3 rdir = rd - 2.0f * (dot(normal, rd)) * normal;
+        const int nb = gb - 1;
+        if (nb == 0) continue;  // second ray cannot hit: colour (0,0,0)
+        unsigned flag = 0u;
+        if (transp) {  // refractionLight(ray, obj) of the OUTER pair (draw.cu:424), weight patched at resume
+          if (sp + 1 < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_REFRACT, gb, 0u)), 0.f, 0.f, 0.f);
+            FR(sp, 1) = make_float4(rd.x, rd.y, rd.z, hp.x);
+            FR(sp, 2) = make_float4(hp.y, hp.z, hn.x, hn.y);
+            FR(sp, 3) = make_float4(hn.z, hior, 0.f, 0.f);
+            sp++; flag = 1u;
+          } else overflow = true;
+        }
+        if (sp < P.depth) {
+          FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_W_REFLECT, nb, flag)), W.x, W.y, W.z); sp++;
+          emit = true; eo = hp + hn * 0.001f; ed = normalize3(rdir); elimit = INFINITY; etag = (unsigned)i;
+        } else { overflow = true; if (flag) sp--; }
+      } else if (gt == T_REFRACT) {  // refractionLight, draw.cu:456-482
+        const float4 g1 = FR(sp, 1), g2 = FR(sp, 2), g3 = FR(sp, 3);
+        const V3 dir = mk3(g1.x, g1.y, g1.z), ip = mk3(g1.w, g2.x, g2.y);
+        const V3 normal = normalize3(mk3(g2.z, g2.w, g3.x));
+        const float ior = 1.0f / g3.y;
+        int bounce = gb;
+        const float k = 1.0f - pow(ior, 2) * (1.0f - pow(dot(normal, dir), 2));
+        if (k < 0) {  // total internal reflection
+          const V3 rdir = dir - 2.0f * (dot(normal, dir)) * normal;
+          --bounce;
+          if (bounce == 0) continue;
+          if (sp < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_W_REFRACT2, bounce, 0u)), W.x, W.y, W.z); sp++;
+            emit = true; eo = ip + normal * 0.001f; ed = normalize3(rdir); elimit = INFINITY; etag = (unsigned)i;
+          } else overflow = true;
+        } else {
+          const V3 rdir = ior * dir - (ior * (dot(normal, dir)) + sqrt(k)) * normal;
+          if (sp < P.depth) {
+            FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_W_REFRACT1, bounce, 0u)), W.x, W.y, W.z); sp++;
+            emit = true; eo = ip - normal * 0.0001f; ed = normalize3(rdir); elimit = INFINITY; etag = (unsigned)i;
+          } else overflow = true;
+        }
+      } else if (gt == T_GI) {  // globalIllumination, draw.cu:540-551
+        const float4 g1 = FR(sp, 1), g2 = FR(sp, 2);
+        const V3 ip = mk3(g1.x, g1.y, g1.z), normal = mk3(g1.w, g2.x, g2.y);
+        NEED_RNG();
+        // spherePoint, helper.cu:91-101
+        const float z = 2.0f * xw_rand(0.0f, 1.0f, rng) - 1.0f;
+        const float theta = 2.0f * 3.14159265f * xw_rand(0.0f, 1.0f, rng);
+        const float rr = sqrt(1.0f - z * z);
+        const V3 spt = mk3(rr * cos(theta), rr * sin(theta), z);
+        const V3 gdir = normalize3(normal + spt);
+        const int nb = gb - 1;
+        if (nb == 0) continue;
+        if (sp < P.depth) {
+          FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_W_GI, nb, 0u)), W.x, W.y, W.z); sp++;
+          emit = true; eo = ip + normal * 0.001f; ed = normalize3(gdir); elimit = INFINITY; etag = (unsigned)i;
+        } else overflow = true;
+      }
+    }
+    B.ctl[i] = (unsigned)sp;
+    if (rng_dirty) rng_store(B, i, rng);
+    if (acc_dirty) B.accum[i] = acc;
+    if (overflow) B.counters[2] = 1u;
+#undef FR
+#undef NEED_RNG
+#undef NEED_ACC
+  }
+  queue_append(qout, B.counters + 1, emit, eo, ed, elimit, etag);
+  const unsigned sm = __ballot_sync(0xffffffffu, shaded);
+  if (sm && (threadIdx.x & 31) == 0) atomicAdd(B.stats + 2, (unsigned long long)__popc(sm));
+}
+
+// ---- resolve: sample sum in the butterfly order of render_kernel_warp_aa, sRGB, 8-bit store -----
+__device__ __forceinline__ float rgb_to_srgb(float l) {  // RGBtosRGB, helper.cu:12-27
+  float sol;
+  if (l < 0.0031308f) sol = 12.92f * l;
+  else sol = 1.055f * pow(l, 1 / 2.4f) - 0.055f;
+  sol = fmin(1.0f, fmax(0.0f, sol));
+  return sol;
+}
+__device__ __forceinline__ unsigned char to_u8_round(float f) {  // floatToUcharWarp, draw.cu:9-11
+  return (unsigned char)(fminf(fmaxf(f, 0.0f), 1.0f) * 255.0f + 0.5f);
+}
+__device__ __forceinline__ float4 add4(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+
+// v[i] += v[i ^ m] for m = NP2/2 .. 1 leaves in v[0] the halving-tree sum: lane 0 of the shuffle butterfly
+// (draw.cu:181-189).  Samples >= spp are zero.
+template <int NP2>
+__device__ __forceinline__ float4 tree_sum(const float4* __restrict__ a, size_t stride, int spp) {
+  float4 v[NP2 / 2 > 0 ? NP2 / 2 : 1];
+  if (NP2 == 1) return a[0];
+#pragma unroll
+  for (int k = 0; k < NP2 / 2; k++) {
+    const float4 lo = k < spp ? a[(size_t)k * stride] : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 hi = k + NP2 / 2 < spp ? a[(size_t)(k + NP2 / 2) * stride] : make_float4(0.f, 0.f, 0.f, 0.f);
+    v[k] = add4(lo, hi);
+  }
+#pragma unroll
+  for (int half = NP2 / 4; half >= 1; half >>= 1) {
+#pragma unroll
+    for (int k = 0; k < half; k++) v[k] = add4(v[k], v[k + half]);
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(128) resolve_kernel(const RenderParams P, const RenderBuffers B, uint8_t* __restrict__ rgba,
+                                                     uint8_t* __restrict__ written) {
+  const int lp = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lp >= P.npix) return;
+  int x, y, pix;
+  if (!slot_to_pixel(P, P.slot0 + lp, x, y, pix)) return;
+  const float4* a = B.accum + lp;
+  uchar4 out;
+  if (P.mode != 2) {  // render_kernel store, draw.cu:129-132 (float -> unsigned char truncates)
+    const float4 c = a[0];
+    out.x = (unsigned char)(rgb_to_srgb(c.x) * 255); out.y = (unsigned char)(rgb_to_srgb(c.y) * 255);
+    out.z = (unsigned char)(rgb_to_srgb(c.z) * 255); out.w = (unsigned char)(c.w * 255);
+  } else {
+    int np2 = 1; while (np2 < P.spp) np2 <<= 1;
+    float4 v;
+    const size_t st = (size_t)P.npix;
+    if (np2 <= 2) v = tree_sum<2>(a, st, P.spp);
+    else if (np2 == 4) v = tree_sum<4>(a, st, P.spp);
+    else if (np2 == 8) v = tree_sum<8>(a, st, P.spp);
+    else if (np2 == 16) v = tree_sum<16>(a, st, P.spp);
+    else if (np2 == 32) v = tree_sum<32>(a, st, P.spp);
+    else if (np2 == 64) v = tree_sum<64>(a, st, P.spp);
+    else {  // in-place halving in global memory (the accumulators are dead after this kernel)
+      float4* w = B.accum + lp;
+      for (int half = np2 / 2; half >= 1; half >>= 1)
+        for (int k = 0; k < half; k++) {
+          const float4 lo = k < P.spp ? w[(size_t)k * st] : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4 hi = k + half < P.spp ? w[(size_t)(k + half) * st] : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (k < P.spp) w[(size_t)k * st] = add4(lo, hi);
+        }
+      v = w[0];
+    }
+    const float inv = 1.0f / (float)P.spp;  // draw.cu:195 (1.0f/32.0f)
+    out.x = to_u8_round(rgb_to_srgb(v.x * inv)); out.y = to_u8_round(rgb_to_srgb(v.y * inv));
+    out.z = to_u8_round(rgb_to_srgb(v.z * inv)); out.w = to_u8_round(v.w * inv);
+  }
+  reinterpret_cast<uchar4*>(rgba)[pix] = out;
+  if (written) written[pix] = 1;
+}
+
+// ---- rt_trace helpers ----------------------------------------------------------------------------
+__global__ void pack_rays_kernel(const float* __restrict__ org, const float* __restrict__ dir, int n, float4* __restrict__ q) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  q[2 * (size_t)i] = make_float4(org[3 * (size_t)i], org[3 * (size_t)i + 1], org[3 * (size_t)i + 2], INFINITY);
+  q[2 * (size_t)i + 1] = make_float4(dir[3 * (size_t)i], dir[3 * (size_t)i + 1], dir[3 * (size_t)i + 2], __uint_as_float((unsigned)i));
+}
+__global__ void unpack_hits_kernel(const float2* __restrict__ hits, const uint32_t* __restrict__ perm, int n, int32_t* __restrict__ ids,
+                                   float* __restrict__ ts) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float2 h = hits[i];
+  int id = __float_as_int(h.y);
+  if (id >= 0) id = (int)perm[(unsigned)id & RT_LEAF_MASK];
+  ids[i] = id;
+  if (ts) ts[i] = id == -1 ? INFINITY : h.x;
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+struct RngTables {  // device copies of the skip-ahead matrices, one set per device
+  uint32_t* mats = nullptr; int mats_count = 0;
+  uint32_t* base = nullptr; int base_count = 0;
+};
+
+struct RenderState {
+  char* pool = nullptr; size_t pool_bytes = 0;
+  uint32_t* counters = nullptr; unsigned long long* stats = nullptr;
+  uint32_t* h_count = nullptr;  // pinned
+  RngTables rng;
+  cudaEvent_t e0 = nullptr, e1 = nullptr, t0 = nullptr, t1 = nullptr;
+  int trav_grid = 0;
+  uint8_t* d_rgba = nullptr; int32_t* d_ids = nullptr; uint8_t* d_written = nullptr; size_t img_px = 0;  // rt_render_host staging
+  float4* trace_q = nullptr; float2* trace_hits = nullptr; size_t trace_cap = 0;
+};
+
+RenderState* get_state(rt_scene* s) {
+  if (!s->rstate) s->rstate = new RenderState();
+  return (RenderState*)s->rstate;
+}
+
+int ensure_common(rt_scene* s, RenderState* st) {
+  if (!st->counters) {
+    RT_CUDA(cudaMalloc(&st->counters, 64));
+    RT_CUDA(cudaMalloc(&st->stats, 64));
+    RT_CUDA(cudaMallocHost(&st->h_count, 64));
+    RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
+    RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
+    int per_sm = 0, sms = 0;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_kernel<false, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
+    if (per_sm < 1) per_sm = 1;
+    st->trav_grid = sms * per_sm;  // persistent grid: every SM full, 148 x resident CTAs on B200
+  }
+  return RT_OK;
+}
+
+int fetch_root(rt_scene* s) {
+  if (s->n > 0 && s->root == INT32_MIN) {
+    RT_CUDA(cudaDeviceSynchronize());
+    RT_CUDA(cudaMemcpy(&s->root, s->bounds + 8, 4, cudaMemcpyDeviceToHost));
+  }
+  return RT_OK;
+}
+
+RtDeviceScene device_scene(const rt_scene* s) {
+  RtDeviceScene d;
+  d.n = s->n; d.root = s->n > 0 ? s->root : 0; d.nodes = s->nodes; d.sorted_tv = s->sorted_tv; d.perm = s->sorted_perm; d.prim_mat = s->prim_mat;
+  d.suns = s->suns; d.num_suns = s->cfg.num_suns; d.bulbs = s->bulbs; d.num_bulbs = s->cfg.num_bulbs;
+  d.planes = s->planes; d.num_planes = s->cfg.num_planes;
+  return d;
+}
+
+template <typename... Args>
+void launch_traverse(bool ref_order, bool count, int grid, cudaStream_t st, Args... args) {
+  if (ref_order) { if (count) traverse_kernel<true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); }
+  else { if (count) traverse_kernel<false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); }
+}
+
+int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
+  if (mats_needed > st->rng.mats_count) {
+    std::vector<uint32_t> h;
+    rt_xorwow_power_matrices(mats_needed, h);
+    if (st->rng.mats) cudaFree(st->rng.mats);
+    RT_CUDA(cudaMalloc(&st->rng.mats, h.size() * 4));
+    RT_CUDA(cudaMemcpy(st->rng.mats, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+    st->rng.mats_count = mats_needed;
+  }
+  if (base_needed > st->rng.base_count) {
+    std::vector<uint32_t> h;
+    rt_xorwow_base_vectors(1234ull, 256, base_needed, h);
+    if (st->rng.base) cudaFree(st->rng.base);
+    RT_CUDA(cudaMalloc(&st->rng.base, h.size() * 4));
+    RT_CUDA(cudaMemcpy(st->rng.base, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+    st->rng.base_count = base_needed;
+  }
+  return RT_OK;
+}
+
+size_t env_size(const char* name, size_t dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return (size_t)strtoull(v, nullptr, 10);
+}
+
+}  // namespace
+
+int rt_render_free_state(rt_scene* s) {
+  RenderState* st = (RenderState*)s->rstate;
+  if (!st) return RT_OK;
+  cudaFree(st->pool); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
+  cudaFree(st->rng.mats); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
+  cudaFree(st->trace_q); cudaFree(st->trace_hits);
+  if (st->e0) { cudaEventDestroy(st->e0); cudaEventDestroy(st->e1); cudaEventDestroy(st->t0); cudaEventDestroy(st->t1); }
+  delete st;
+  s->rstate = nullptr;
+  return RT_OK;
+}
+
+extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles, uint8_t* d_rgba, int32_t* d_hit_id,
+                         uint8_t* d_written, rt_counters* counters, void* stream) {
+  if (!s || !d_rgba) { rt_set_error("rt_render: null argument"); return RT_ERR_INVALID; }
+  if (w <= 0 || h <= 0 || (long long)w * h > 0x7FFFFFFFll / 64) { rt_set_error("rt_render: bad image size"); return RT_ERR_INVALID; }
+  if (s->n > 0 && !s->built) { rt_set_error("rt_render: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
+  if (tiles && (tiles->tile_w <= 0 || tiles->tile_h <= 0 || tiles->num_ranks <= 0 || tiles->rank < 0 || tiles->rank >= tiles->num_ranks)) {
+    rt_set_error("rt_render: bad tile set"); return RT_ERR_INVALID;
+  }
+  RT_CUDA(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  RenderState* rs = get_state(s);
+  int rc = ensure_common(s, rs); if (rc) return rc;
+  rc = fetch_root(s); if (rc) return rc;
+
+  RenderParams P; memset(&P, 0, sizeof(P));
+  RtCamera& C = P.cam;
+  C.width = w; C.height = h; C.bounces = s->cfg.bounces; C.gi = s->cfg.gi; C.dof_focus = s->cfg.dof_focus; C.dof_lens = s->cfg.dof_lens;
+  C.expose = s->cfg.expose; C.fisheye = s->cfg.fisheye; C.panorama = s->cfg.panorama;
+  for (int k = 0; k < 3; k++) { C.forward[k] = s->cfg.forward[k]; C.right[k] = s->cfg.right[k]; C.up[k] = s->cfg.up[k]; C.eye[k] = s->cfg.eye[k]; }
+  P.W = w; P.H = h;
+  const long long npx = (long long)w * h;
+  if (aa <= 1) { P.mode = aa <= 0 ? 0 : 1; P.spp = 1; P.covered = (int)npx; }
+  else {
+    P.mode = 2;
+    if (flags & RT_SPP_TRUE) { P.spp = aa; P.covered = (int)npx; }
+    else {  // render(), draw.cu:226-238: ceil(P*aa/128) blocks of 4 warps, one warp = one pixel, 32 samples
+      P.spp = 32;
+      const long long grid = (npx * aa + 127) / 128;
+      P.covered = (int)std::min<long long>(npx, grid * 4);
+    }
+  }
+  if (tiles) { P.tile_w = std::min(tiles->tile_w, w); P.tile_h = std::min(tiles->tile_h, h); P.num_ranks = tiles->num_ranks; P.rank = tiles->rank; }
+  else { P.tile_w = w; P.tile_h = h; P.num_ranks = 1; P.rank = 0; }
+  P.tiles_x = (w + P.tile_w - 1) / P.tile_w;
+  const int tiles_y = (h + P.tile_h - 1) / P.tile_h;
+  const long long ntiles = (long long)P.tiles_x * tiles_y;
+  const long long owned = ntiles > P.rank ? (ntiles - P.rank + P.num_ranks - 1) / P.num_ranks : 0;
+  P.slots_per_tile = P.tile_w * P.tile_h;
+  long long nslots = owned * P.slots_per_tile;
+  if (!tiles) nslots = P.covered;  // one tile = the image: slot == pixel
+  P.ref_order = (flags & RT_TRAVERSE_NEAR_FIRST) ? 0 : 1;
+  P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
+  const bool count = (flags & RT_COUNTERS) != 0;
+  const bool both = s->any_shiny && s->any_trans;
+  const int gi = s->cfg.gi != 0 ? 1 : 0;
+  P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
+  if (P.depth > 200) { rt_set_error("rt_render: bounces too large for the continuation stack"); return RT_ERR_INVALID; }
+  P.need_rng = (P.mode != 0) || s->cfg.dof_focus != 0.0f || s->any_rough || s->cfg.gi != 0;
+  if (s->cfg.fisheye || s->cfg.panorama) { if (P.mode == 0 && !s->any_rough && s->cfg.gi == 0) P.need_rng = 0; }
+  P.num_lights = s->cfg.num_suns + s->cfg.num_bulbs;
+
+  // RNG tables
+  if (P.mode == 2) { rc = ensure_rng_tables(rs, std::max(32, P.spp), 0); if (rc) return rc; }
+  else if (P.need_rng) { rc = ensure_rng_tables(rs, 256, (int)((npx + 255) / 256)); if (rc) return rc; }
+
+  // pass size: all per-sample state lives in one pool
+  const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8;
+  const size_t budget = env_size("RT_POOL_BYTES", (size_t)6 << 30);
+  const long long total_samples = nslots * P.spp;
+  long long max_s = (long long)(budget / per_sample);
+  long long npix_pass = std::max<long long>(1, max_s / P.spp);
+  if (npix_pass >= nslots) npix_pass = nslots;
+  else npix_pass = std::max<long long>(32, npix_pass & ~31ll);
+  if (nslots == 0) npix_pass = 0;
+  const size_t Smax = (size_t)npix_pass * P.spp;
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t need = al(Smax * 16) * 2 + al(Smax * 16) + al(Smax * 4) + al(Smax * 64 * P.depth) + al(Smax * 32) * 2 + al(Smax * 8) + 4096;
+  if (need > rs->pool_bytes) {
+    if (rs->pool) cudaFree(rs->pool);
+    rs->pool = nullptr; rs->pool_bytes = 0;
+    cudaError_t e = cudaMalloc((void**)&rs->pool, need);
+    if (e != cudaSuccess) { rt_set_error(std::string("rt_render: state pool cudaMalloc: ") + cudaGetErrorString(e)); return RT_ERR_NOMEM; }
+    rs->pool_bytes = need;
+  }
+  RenderBuffers B; memset(&B, 0, sizeof(B));
+  {
+    char* p = rs->pool;
+    B.rng0 = (uint4*)p; p += al(Smax * 16); B.rng1 = (uint4*)p; p += al(Smax * 16);
+    B.accum = (float4*)p; p += al(Smax * 16); B.ctl = (uint32_t*)p; p += al(Smax * 4);
+    B.frames = (float4*)p; p += al(Smax * 64 * P.depth);
+    B.qa = (float4*)p; p += al(Smax * 32); B.qb = (float4*)p; p += al(Smax * 32);
+    B.hits = (float2*)p; p += al(Smax * 8);
+  }
+  B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_base = rs->rng.base;
+  const RtDeviceScene sc = device_scene(s);
+
+  RT_CUDA(cudaEventRecord(rs->e0, st));
+  RT_CUDA(cudaMemsetAsync(d_rgba, 0, (size_t)npx * 4, st));
+  if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, st));
+  if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, st));
+  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, st));
+  uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f;
+  for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
+    P.slot0 = (int)slot0; P.npix = (int)std::min<long long>(npix_pass, nslots - slot0); P.S = P.npix * P.spp;
+    passes++;
+    samples += (uint64_t)P.S;
+    RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+    if (P.mode != 2 && P.need_rng) {
+      const int hn = (int)(((npx + 255) / 256 + 31) & ~31ll);
+      rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, st>>>(P, B, hn);
+      launches++;
+    }
+    generate_kernel<<<(unsigned)((P.S + 255) / 256), 256, 0, st>>>(P, B, B.qa, d_hit_id);
+    launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 4, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    unsigned n_in = rs->h_count[0];
+    float4 *qin = B.qa, *qout = B.qb;
+    while (n_in > 0) {
+      iters++; rays += n_in;
+      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+      if (count) RT_CUDA(cudaEventRecord(rs->t0, st));
+      const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n_in + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
+      launch_traverse(P.ref_order != 0, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats);
+      if (count) RT_CUDA(cudaEventRecord(rs->t1, st));
+      shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
+      launches += 2;
+      RT_CUDA(cudaGetLastError());
+      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 8, cudaMemcpyDeviceToHost, st));
+      RT_CUDA(cudaStreamSynchronize(st));
+      if (count) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
+      n_in = rs->h_count[0];
+      if (rs->h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
+      std::swap(qin, qout);
+    }
+    resolve_kernel<<<(P.npix + 127) / 128, 128, 0, st>>>(P, B, d_rgba, d_written);
+    launches++;
+    RT_CUDA(cudaGetLastError());
+  }
+  RT_CUDA(cudaEventRecord(rs->e1, st));
+  RT_CUDA(cudaEventSynchronize(rs->e1));
+  if (counters) {
+    memset(counters, 0, sizeof(*counters));
+    counters->rays = rays; counters->samples = samples; counters->wavefront_iters = iters; counters->passes = passes;
+    counters->kernel_launches = launches; counters->traverse_ms = trav_ms;
+    RT_CUDA(cudaEventElapsedTime(&counters->render_ms, rs->e0, rs->e1));
+    unsigned long long hs[3];
+    RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
+    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1]; counters->shaded_hits = hs[2];
+  }
+  (void)total_samples;
+  return RT_OK;
+}
+
+extern "C" int rt_render_host(rt_scene* s, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles, uint8_t* h_rgba, int32_t* h_hit_id,
+                              uint8_t* h_written, rt_counters* counters) {
+  if (!s || !h_rgba) { rt_set_error("rt_render_host: null argument"); return RT_ERR_INVALID; }
+  if (w <= 0 || h <= 0) { rt_set_error("rt_render_host: bad image size"); return RT_ERR_INVALID; }
+  RT_CUDA(cudaSetDevice(s->device));
+  RenderState* rs = get_state(s);
+  const size_t npx = (size_t)w * h;
+  if (npx > rs->img_px) {
+    cudaFree(rs->d_rgba); cudaFree(rs->d_ids); cudaFree(rs->d_written);
+    rs->d_rgba = nullptr; rs->d_ids = nullptr; rs->d_written = nullptr; rs->img_px = 0;
+    RT_CUDA(cudaMalloc(&rs->d_rgba, npx * 4)); RT_CUDA(cudaMalloc(&rs->d_ids, npx * 4)); RT_CUDA(cudaMalloc(&rs->d_written, npx));
+    rs->img_px = npx;
+  }
+  const int rc = rt_render(s, w, h, aa, flags, tiles, rs->d_rgba, h_hit_id ? rs->d_ids : nullptr, h_written ? rs->d_written : nullptr, counters, nullptr);
+  if (rc) return rc;
+  RT_CUDA(cudaMemcpy(h_rgba, rs->d_rgba, npx * 4, cudaMemcpyDeviceToHost));  // main.cu:77
+  if (h_hit_id) RT_CUDA(cudaMemcpy(h_hit_id, rs->d_ids, npx * 4, cudaMemcpyDeviceToHost));
+  if (h_written) RT_CUDA(cudaMemcpy(h_written, rs->d_written, npx, cudaMemcpyDeviceToHost));
+  return RT_OK;
+}
+
+extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_dir, unsigned flags, int32_t* d_hit_id, float* d_hit_t,
+                        rt_counters* counters, void* stream) {
+  if (!s || !d_org || !d_dir || !d_hit_id || n < 0) { rt_set_error("rt_trace: bad argument"); return RT_ERR_INVALID; }
+  if (s->n > 0 && !s->built) { rt_set_error("rt_trace: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
+  RT_CUDA(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  RenderState* rs = get_state(s);
+  int rc = ensure_common(s, rs); if (rc) return rc;
+  rc = fetch_root(s); if (rc) return rc;
+  if (n == 0) return RT_OK;
+  if ((size_t)n > rs->trace_cap) {
+    cudaFree(rs->trace_q); cudaFree(rs->trace_hits); rs->trace_q = nullptr; rs->trace_hits = nullptr; rs->trace_cap = 0;
+    RT_CUDA(cudaMalloc(&rs->trace_q, (size_t)n * 32)); RT_CUDA(cudaMalloc(&rs->trace_hits, (size_t)n * 8));
+    rs->trace_cap = (size_t)n;
+  }
+  const bool count = (flags & RT_COUNTERS) != 0;
+  const RtDeviceScene sc = device_scene(s);
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
+  pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
+  RT_CUDA(cudaEventRecord(rs->e0, st));
+  const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
+  launch_traverse((flags & RT_TRAVERSE_NEAR_FIRST) == 0, count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats);
+  RT_CUDA(cudaEventRecord(rs->e1, st));
+  unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(rs->trace_hits, s->sorted_perm, n, d_hit_id, d_hit_t);
+  RT_CUDA(cudaGetLastError());
+  if (counters) {
+    RT_CUDA(cudaStreamSynchronize(st));
+    memset(counters, 0, sizeof(*counters));
+    counters->rays = (uint64_t)n; counters->kernel_launches = 3;
+    RT_CUDA(cudaEventElapsedTime(&counters->traverse_ms, rs->e0, rs->e1));
+    counters->render_ms = counters->traverse_ms;
+    unsigned long long hs[3];
+    RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
+    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1];
+  }
+  return RT_OK;
 }

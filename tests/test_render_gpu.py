@@ -1,0 +1,266 @@
+"""GPU parity of traversal + shading against the CPU oracle.
+
+Closest-hit ids (and hit distances) must be bit-exact; deterministic 1-sample images must agree within
+1/255 per channel; multi-sample images within 1/255 as well here (PSNR is reported), because both sides
+replay the same per-sample XORWOW stream.  Scenes whose ray generation or normals go through
+transcendental functions that differ between libm and libdevice (DOF cos/sin, rough-surface Box-Muller)
+are compared statistically here and exactly against the reference's own CUDA build in
+test_vs_reference_gpu.py."""
+import numpy as np
+import pytest
+
+import helpers as H
+import oracle_lib as O
+from cuda_ray_tracer_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def built_pair(o, mode=O.BOUNDS_COMPUTED, bits=30):
+    o.build(mode, bits)
+    sc = H.gpu_scene_from_oracle(o, mode)
+    sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED if mode == O.BOUNDS_COMPUTED else api.BOUNDS_FROM_DESC)
+    return sc
+
+
+def random_rays(n, seed, origin_scale=3.0):
+    rng = np.random.RandomState(seed)
+    org = rng.uniform(-origin_scale, origin_scale, (n, 3)).astype(np.float32)
+    tgt = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+    d = tgt - org
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return org, d
+
+
+def gpu_trace(sc, org, d, flags=0):
+    import torch
+    to, td = torch.from_numpy(org).cuda(), torch.from_numpy(d).cuda()
+    ids = torch.empty(len(org), dtype=torch.int32, device="cuda"); ts = torch.empty(len(org), dtype=torch.float32, device="cuda")
+    cnt = api.Counters()
+    sc.trace_device(len(org), to, td, ids, ts, flags=flags, counters=cnt)
+    torch.cuda.synchronize()
+    return ids.cpu().numpy(), ts.cpu().numpy(), cnt
+
+
+def check_trace(gi, gt, ids, ts, flags):
+    bad = (gi != ids).sum()
+    if flags & api.TRAVERSE_NEAR_FIRST:  # see compare_render
+        assert bad <= 1e-3 * len(ids), "near-first closest-hit ids differ: %d of %d" % (bad, len(ids))
+        same = gi == ids
+        assert np.array_equal(gt[same].view(np.uint32), ts[same].view(np.uint32))
+    else:
+        assert bad == 0, "closest-hit ids differ: %d of %d" % (bad, len(ids))
+        assert np.array_equal(gt.view(np.uint32), ts.view(np.uint32)), "hit distances differ"
+
+
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+@pytest.mark.parametrize("mode", [O.BOUNDS_COMPUTED, O.BOUNDS_SHIPPED])
+def test_trace_ids_mixed_scene(flags, mode):
+    cfg, a = H.mixed_scene(3000)
+    a["planes"] = np.array([[0, 1, 0, 1.2] + [0, 1, 0] + [0, -1.2, 0] + [0.5, 0.5, 0.5, 0, 0, 0, 0, 0, 0, 1.458, 0]], np.float32)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o, mode)
+    org, d = random_rays(20000, 1)
+    ids, ts, _ = o.trace(org, d)
+    gi, gt, cnt = gpu_trace(sc, org, d, flags | api.COUNTERS)
+    check_trace(gi, gt, ids, ts, flags)
+    assert cnt.nodes_visited > 0 and cnt.leaf_tests > 0
+
+
+@pytest.mark.parametrize("name", ["tri", "redchair", "tenthousand", "spiral"])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+def test_trace_ids_scene_files(name, flags):
+    p = H.scene_path(name)
+    if p is None:
+        pytest.skip("scene fixtures not present")
+    o = O.OracleScene(p)
+    sc = built_pair(o)
+    org, d = random_rays(20000, 2, 2.0)
+    ids, ts, _ = o.trace(org, d)
+    gi, gt, _ = gpu_trace(sc, org, d, flags)
+    check_trace(gi, gt, ids, ts, flags)
+
+
+def test_ref_order_node_counts_match_oracle():
+    """in the reference's visiting order the kernel performs exactly the oracle's box and primitive tests"""
+    cfg, a = synth.soup(5000, seed=4, width=32, height=32, aa=0)
+    a = synth.finish_triangles(a)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o)
+    org, d = random_rays(5000, 3)
+    ids, ts, oc = o.trace(org, d)
+    gi, gt, cnt = gpu_trace(sc, org, d, api.COUNTERS)
+    assert np.array_equal(gi, ids)
+    assert cnt.leaf_tests == oc.leaf_tests
+    assert cnt.nodes_visited + cnt.leaf_tests == oc.nodes_visited  # the oracle counts leaf visits as node visits
+
+
+def compare_render(o, sc, w, h, aa, spp_mode=O.SPP_REF, flags=0, tol=1, frac_ok=1.0, ids_exact=True):
+    if flags & api.TRAVERSE_NEAR_FIRST and frac_ok >= 1.0:
+        # near-first may differ from the reference's visiting order where a hit lies outside its own AABB
+        # (triangle test tolerance): rare, never more than a handful of pixels
+        frac_ok = 0.99; ids_exact = False; near = True
+    else:
+        near = False
+    r = o.render(w, h, aa, spp_mode)
+    g = sc.render(w, h, aa, flags | (api.SPP_TRUE if spp_mode == O.SPP_TRUE else 0), want_ids=True, want_written=True)
+    assert np.array_equal(g["written"], r["written"]), "covered pixel set differs"
+    m = r["written"].astype(bool)
+    bad = (g["ids"][m] != r["ids"][m]).sum()
+    if ids_exact:
+        assert bad == 0, "primary closest-hit ids differ at %d pixels" % bad
+    elif near:
+        assert bad <= 2e-3 * m.sum() + 1, "near-first closest-hit ids differ at %d pixels" % bad
+    d = np.abs(g["rgba"].astype(np.int32) - r["rgba"].astype(np.int32))[m]
+    ok = (d.max(axis=-1) <= tol).mean() if d.size else 1.0
+    assert ok >= frac_ok, "only %.4f of pixels within %d/255 (max diff %d)" % (ok, tol, d.max())
+    assert (g["rgba"][~m] == 0).all()
+    if frac_ok >= 1.0 and ids_exact:
+        assert g["counters"].rays == r["counters"].rays, "ray count differs from the oracle's hitNearest count"
+    return g, r
+
+
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+def test_render_tri_scene(flags):
+    p = H.scene_path("tri")
+    if p is None:
+        pytest.skip("scene fixtures not present")
+    o = O.OracleScene(p)
+    for mode in (O.BOUNDS_SHIPPED, O.BOUNDS_COMPUTED):
+        sc = built_pair(o, mode)
+        g, r = compare_render(o, sc, 100, 100, 0, flags=flags)
+        assert (g["ids"] >= 0).sum() == 3138  # covered pixels of the reference's tri.txt
+
+
+@pytest.mark.parametrize("aa,spp_mode", [(0, O.SPP_REF), (1, O.SPP_REF), (32, O.SPP_REF), (20, O.SPP_REF), (5, O.SPP_TRUE), (16, O.SPP_TRUE)])
+def test_render_redchair_modes(aa, spp_mode):
+    """redchair.txt: 1715 triangles + a transparent+shiny and a mirror sphere, plane, 2 suns, gi 2, expose"""
+    p = H.scene_path("redchair")
+    if p is None:
+        pytest.skip("scene fixtures not present")
+    o = O.OracleScene(p)
+    sc = built_pair(o)
+    w, h = (96, 96) if aa <= 1 else (40, 40)
+    g, r = compare_render(o, sc, w, h, aa, spp_mode, flags=0)
+    assert g["counters"].rays == r["counters"].rays, "ray count differs from the oracle's hitNearest count"
+    g2, _ = compare_render(o, sc, w, h, aa, spp_mode, flags=api.TRAVERSE_NEAR_FIRST)
+    assert (np.abs(g2["rgba"].astype(int) - g["rgba"].astype(int)).max(axis=-1) > 1).mean() < 1e-2, "near-first traversal changed the image"
+
+
+def synthetic_full_featured(n=4000, seed=11, rough=0.0):
+    """spheres + triangles with shiny / transparent / both materials, a plane, a sun and a bulb, gi 2"""
+    cfg, a = H.mixed_scene(n, seed)
+    rng = np.random.RandomState(seed)
+    for key in ("tri_mat", "sphere_mat"):
+        m = a[key]
+        k = rng.randint(0, 6, len(m))
+        m[k == 1, 3:6] = 0.6                       # shiny
+        m[k == 2, 6:9] = 0.7                       # transparent
+        m[k == 3, 3:6] = 0.3; m[k == 3, 6:9] = 0.5  # both
+        if rough:
+            m[k == 4, 10] = rough
+    a["planes"] = np.array([[0, 1, 0, 1.3] + [0, 1, 0] + [0, -1.3, 0] + [0.6, 0.6, 0.7, 0.2, 0.2, 0.2, 0, 0, 0, 1.458, 0]], np.float32)
+    a["suns"] = np.array([[1, 2, 1.5, 1, 1, 0.9]], np.float32)
+    a["bulbs"] = np.array([[0.3, 1.1, 2.5, 3.0, 2.5, 2.0]], np.float32)
+    cfg.update(eye=(0, 0, 3.2), bounces=4, gi=2, expose=1.5)
+    return cfg, a
+
+
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+def test_render_all_shading_paths(flags):
+    cfg, a = synthetic_full_featured()
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o)
+    g, r = compare_render(o, sc, 80, 60, 0, flags=flags)
+    assert g["counters"].rays > 80 * 60  # secondary rays were traced
+    compare_render(o, sc, 32, 24, 32, flags=flags)
+
+
+@pytest.mark.parametrize("zyx", [0, 1])
+def test_render_rough_materials(zyx):
+    """rough surfaces draw curand_normal values; Box-Muller uses __sincosf on the device and sinf/cosf in the
+    oracle, so a few pixels at silhouettes may differ — the RNG stream order itself is checked by the rest"""
+    cfg, a = synthetic_full_featured(rough=0.05)
+    o = H.oracle_from_arrays(cfg, a)
+    O.lib().o_set_args_rtl(zyx)
+    try:
+        sc = built_pair(o)
+        compare_render(o, sc, 80, 60, 0, flags=(api.ROUGH_ZYX if zyx else 0), tol=1, frac_ok=0.97)
+        compare_render(o, sc, 32, 24, 32, flags=(api.ROUGH_ZYX if zyx else 0), tol=2, frac_ok=0.97)
+    finally:
+        O.lib().o_set_args_rtl(0)
+
+
+def test_render_camera_modes():
+    cfg, a = synth.soup(3000, seed=2, width=64, height=48, aa=0)
+    a = synth.finish_triangles(a)
+    for extra in (dict(fisheye=1), dict(panorama=1), dict(dof_focus=3.0, dof_lens=0.05), dict(bounces=0), dict(bounces=1)):
+        c = dict(cfg); c.update(extra)
+        o = H.oracle_from_arrays(c, a)
+        sc = built_pair(o)
+        exact = not any(k in extra for k in ("panorama", "dof_focus", "fisheye"))  # cos/sin/pow differ between libm and libdevice
+        compare_render(o, sc, 64, 48, 0, ids_exact=exact, frac_ok=1.0 if exact else 0.98)
+        compare_render(o, sc, 64, 48, 1, ids_exact=exact, frac_ok=1.0 if exact else 0.98)
+
+
+def test_render_soup_and_spheres_bigger():
+    for gen in (synth.soup, synth.spheres):
+        cfg, a = gen(100_000, seed=1, width=160, height=120, aa=0)
+        a = synth.finish_triangles(a)
+        o = H.oracle_from_arrays(cfg, a)
+        sc = built_pair(o)
+        g, r = compare_render(o, sc, 160, 120, 0)
+        assert (g["ids"] >= 0).mean() > 0.1
+        compare_render(o, sc, 48, 32, 16, O.SPP_TRUE)
+
+
+def test_tiles_partition_is_invariant():
+    """image bytes for 1, 2, 4, 8 ranks (interleaved tiles) are identical: RNG is keyed by global pixel index"""
+    cfg, a = synthetic_full_featured(2000, 5)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o)
+    for aa, flags, (w, h) in ((0, 0, (100, 70)), (32, 0, (50, 30)), (6, api.SPP_TRUE, (50, 30)), (20, 0, (50, 30))):
+        full = sc.render(w, h, aa, flags, want_ids=True, want_written=True)
+        for ranks in (2, 4, 8):
+            acc = np.zeros_like(full["rgba"]); wr = np.zeros_like(full["written"]); ids = np.full_like(full["ids"], -1)
+            rays = 0
+            for rank in range(ranks):
+                t = api.TileSet(32, 8, ranks, rank)
+                part = sc.render(w, h, aa, flags, tiles=t, want_ids=True, want_written=True)
+                assert not (wr & part["written"]).any(), "two ranks wrote the same pixel"
+                acc += part["rgba"]; wr |= part["written"]; ids = np.maximum(ids, part["ids"]); rays += part["counters"].rays
+            assert np.array_equal(acc, full["rgba"]) and np.array_equal(wr, full["written"])
+            assert rays == full["counters"].rays
+
+
+def test_multi_pass_equals_single_pass(monkeypatch):
+    cfg, a = synthetic_full_featured(2000, 6)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o)
+    one = sc.render(64, 48, 32)
+    monkeypatch.setenv("RT_POOL_BYTES", str(300_000))  # forces many small passes
+    sc2 = built_pair(o)
+    many = sc2.render(64, 48, 32)
+    assert many["counters"].passes > 4
+    assert np.array_equal(one["rgba"], many["rgba"]) and one["counters"].rays == many["counters"].rays
+
+
+def test_render_requires_build_and_reports_errors():
+    cfg, a = synth.soup(100, seed=1, width=16, height=16, aa=0)
+    a = synth.finish_triangles(a)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = H.gpu_scene_from_oracle(o, O.BOUNDS_COMPUTED)
+    with pytest.raises(api.RtError, match="rt_build_lbvh has not run"):
+        sc.render(16, 16, 0)
+
+
+def test_planes_only_scene():
+    o = O.OracleScene()
+    o.set_config(width=40, height=30, eye=np.array([0, 1, 0], np.float32))
+    o.add_plane([0, 1, 0, 0], np.array([0.8, 0.7, 0.6, 0, 0, 0, 0, 0, 0, 1.458, 0], np.float32))
+    o.add_sun([0.2, 1, 0.3])
+    sc = H.gpu_scene_from_oracle(o, O.BOUNDS_COMPUTED)
+    r = o.render(40, 30, 0)
+    g = sc.render(40, 30, 0, want_ids=True)
+    assert np.array_equal(g["ids"], r["ids"]) and (g["ids"] == -2).any()
+    assert np.abs(g["rgba"].astype(int) - r["rgba"].astype(int)).max() <= 1
