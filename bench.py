@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: Mrays/s on a 1M-triangle soup rendered at 4K, LBVH rebuilt every frame.
+
+One "step" = one frame of the hot path: new vertex positions -> rt_scene_update_triangles (Triangle
+constructor on the device) -> rt_build_lbvh (K1..K6) -> rt_render (generate / traverse / shade / resolve).
+`value` times it with the frame's vertices already resident in HBM and the image left on the device;
+`e2e` times the same frame through the host-buffer entry points (pinned host vertices in, image out).
+With N > 1 the scene is replicated, the image is split into interleaved 32x8 tiles (tile t -> rank t % N)
+and the framebuffer is summed onto rank 0 over NCCL inside the timed region: total work is fixed, so
+scaling is "strong".
+
+`--impl reference` times the reference's own traversal + shading sources compiled for the host
+(oracle/_ref/libref_host.so, all host threads) on a bounded sample of rows of the same frame; the fork has
+no CPU renderer and no way to run without CUDA, so this is its hot path on the box's host cores."""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "Mrays/s @4K, 1M tris + LBVH build ms"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--spp", type=int, default=16)
+    ap.add_argument("--near-first", action="store_true", help="RT_TRAVERSE_NEAR_FIRST lane (not bit-exact in rare cases)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "soup(N=%d,seed=1) %dx%d %dspp (true-spp), 1 sun, LBVH rebuilt every frame (vertices jittered per frame)" % (
+        a.tris, a.width, a.height, a.spp)
+
+
+def frame_vertices(arrays, frame):
+    """vertex positions of frame `frame`: the soup displaced by a deterministic per-frame offset field"""
+    p0, p1, p2 = arrays["tri"][:3]
+    ph = np.float32(0.37 * (frame + 1))
+    d = (np.float32(0.002) * np.sin(p0 * np.float32(7.0) + ph)).astype(np.float32)
+    return (p0 + d).astype(np.float32), (p1 + d).astype(np.float32), (p2 + d).astype(np.float32)
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index; self.rows = []; self.stop_flag = False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(a):
+    """reference arm: the reference's own hitNearest / shootPrimaryRay / curand path on the host cores"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle_lib as O
+    import ref_lib as R
+    import helpers as H
+    from cuda_ray_tracer_b200 import synth
+    kind = "reference" if R.available() else "port"
+    cores = os.cpu_count() or 1
+    cfg, arrays = synth.soup(a.tris, 1, a.width, a.height, a.spp)
+    p0, p1, p2 = frame_vertices(arrays, 0)
+    arrays["tri"] = [p0, p1, p2, None, None, None]
+    nor, e1, e2 = O.triangle_setup(p0, p1, p2)
+    arrays["tri"] = [p0, p1, p2, nor, e1, e2]
+    o = H.oracle_from_arrays(cfg, arrays)
+    t0 = time.time(); b = o.build(O.BOUNDS_COMPUTED, 30); build_s = time.time() - t0  # K1..K6 are __global__ code: CPU restatement
+    ref = None
+    if kind == "reference":
+        ref = R.scene_from_arrays(cfg, arrays); ref.set_bvh(b)
+    W, Hh, spp = a.width, a.height, a.spp
+    # the reference's render() runs 32 samples per pixel whenever aa >= 2; a row of the image is
+    # W*32 primary samples there and W*spp here.  Sample = a band of rows through the middle of the image.
+    ref_spp = 32 if spp >= 2 else 1
+
+    def render_rows(y0, y1):
+        t = time.time()
+        if ref is not None:
+            ref.render(W, Hh, spp if spp < 2 else 32, y0, y1, cores)
+        else:
+            o.render(W, Hh, spp if spp < 2 else 32, O.SPP_REF, y0, y1, cores)
+        return time.time() - t
+
+    def count_rays(y0, y1):  # the reference carries no ray counter: the oracle port counts hitNearest calls of the same rows
+        return o.render(W, Hh, spp if spp < 2 else 32, O.SPP_REF, y0, y1, cores)["counters"].rays
+
+    mid = Hh // 2
+    t_probe = render_rows(mid, mid + 1)
+    total_steps = a.steps + a.warmup
+    rows = max(1, min(Hh // 4, int(a.cpu_seconds * 4 / max(t_probe, 1e-3) / max(total_steps, 1))))
+    vals = []; secs = []
+    for s in range(total_steps):
+        y0 = max(0, min(Hh - rows, mid - rows // 2 + s)); y1 = y0 + rows
+        dt = render_rows(y0, y1)
+        rays = count_rays(y0, y1)
+        if s >= a.warmup:
+            vals.append(rays / dt / 1e6); secs.append(dt)
+    v = float(np.mean(vals))
+    line = {"metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": float(np.mean(secs)) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "reference",
+            "config": {"workload": workload_name(a), "sample": "%d rows of the frame at %d spp per step" % (rows, ref_spp)},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind,
+                             "sample": "%d image rows x %d px x %d spp per step (reference render() semantics), BVH from the CPU restatement of K1..K6 (%.2f s, 1 core)" % (rows, W, ref_spp, build_s)},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(a, cfg, arrays):
+    import oracle_lib as O
+    import ref_lib as R
+    import helpers as H
+    cores = os.cpu_count() or 1
+    p0, p1, p2 = frame_vertices(arrays, 0)
+    nor, e1, e2 = O.triangle_setup(p0, p1, p2)
+    arr = dict(arrays); arr["tri"] = [p0, p1, p2, nor, e1, e2]
+    o = H.oracle_from_arrays(cfg, arr)
+    b = o.build(O.BOUNDS_COMPUTED, 30)
+    kind = "port"; ref = None
+    if R.available():
+        kind = "reference"; ref = R.scene_from_arrays(cfg, arr); ref.set_bvh(b)
+    W, Hh = a.width, a.height
+    aa = a.spp if a.spp < 2 else 32
+    mid = Hh // 2
+
+    def go(y0, y1):
+        t = time.time()
+        if ref is not None:
+            ref.render(W, Hh, aa, y0, y1, cores)
+        else:
+            o.render(W, Hh, aa, O.SPP_REF, y0, y1, cores)
+        return time.time() - t
+
+    t_probe = go(mid, mid + 1)
+    rows = max(1, min(Hh // 8, int(a.cpu_seconds / max(t_probe, 1e-3))))
+    dt = go(mid, mid + rows)
+    rays = o.render(W, Hh, aa, O.SPP_REF, mid, mid + rows, cores)["counters"].rays
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
+            "sample": "%d image rows x %d px x %d spp (reference render() semantics) = %d rays in %.1f s" % (rows, W, aa, rays, dt)}
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from cuda_ray_tracer_b200 import api, synth
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    api.load_library()  # raises when libb200rt.so is missing: there is no fallback
+
+    cfg, arrays = synth.soup(a.tris, 1, a.width, a.height, a.spp)
+    W, Hh, spp, n = a.width, a.height, a.spp, a.tris
+    # scene arrays: rank 0 generates, NCCL broadcasts (scene replication)
+    p0, p1, p2 = arrays["tri"][:3]
+    tp = [torch.from_numpy(x).to(dev) for x in (p0, p1, p2)]
+    tm = torch.from_numpy(arrays["tri_mat"]).to(dev)
+    if world > 1:
+        for t in tp + [tm]:
+            dist.broadcast(t, 0)
+    nor, e1, e2 = api.triangle_setup(p0, p1, p2)
+    arrays["tri"] = [tp[0], tp[1], tp[2]] + [torch.from_numpy(x).to(dev) for x in (nor, e1, e2)]
+    arrays["tri_mat"] = tm
+    arrays["refs"] = torch.from_numpy(arrays["refs"]).to(dev)
+    desc, keep = api.make_desc(cfg, arrays)
+    sc = api.Scene(desc, local)
+
+    nframes = 4
+    frames_h = [frame_vertices({"tri": [p0, p1, p2]}, f) for f in range(nframes)]
+    frames_pinned = [[torch.from_numpy(x).pin_memory() for x in fr] for fr in frames_h]
+    frames_d = [[torch.from_numpy(x).to(dev) for x in fr] for fr in frames_h]
+    img_d = torch.zeros((Hh, W, 4), dtype=torch.uint8, device=dev)
+    img_h = torch.zeros((Hh, W, 4), dtype=torch.uint8).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    tiles = api.TileSet(32, 8, world, rank) if world > 1 else None
+    rflags = api.SPP_TRUE | api.TIME_TRAVERSE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0)
+    BUILD_LAUNCHES = 1 + 8  # update_tris + init, bounds, morton, 4 onesweep passes, bottom-up
+
+    def step_device(f, cnt):
+        fr = frames_d[f % nframes]
+        sc.update_triangles(fr[0], fr[1], fr[2])
+        bms = sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+        sc.render_device(W, Hh, spp, img_d, flags=rflags, tiles=tiles, counters=cnt)
+        if world > 1:
+            dist.reduce(img_d, 0, op=dist.ReduceOp.SUM)  # tiles are disjoint and the rest is zero: sum == gather
+        return bms
+
+    def step_host(f, cnt):
+        fr = frames_pinned[f % nframes]
+        sc.update_triangles(fr[0], fr[1], fr[2])   # host pointers: H2D inside
+        bms = sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+        if world > 1:
+            sc.render_device(W, Hh, spp, img_d, flags=rflags, tiles=tiles, counters=cnt)
+            dist.reduce(img_d, 0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                img_h.copy_(img_d)
+        else:
+            sc.render_host_into(img_h, W, Hh, spp, flags=rflags, counters=cnt)
+        return bms
+
+    def timed(fn, steps, warmup):
+        cnt = api.Counters()
+        for f in range(warmup):
+            fn(f, cnt); flush.fill_(f & 255)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = []; rays = 0; bms = []; trav_ms = 0.0; trav_launches = 0; launches = 0
+        for f in range(steps):
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            b = fn(warmup + f, cnt)
+            e1.record(); torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1)); bms.append(b); rays += cnt.rays
+            trav_ms += cnt.traverse_ms; trav_launches += cnt.traverse_launches; launches += cnt.kernel_launches + BUILD_LAUNCHES
+            flush.fill_(f & 255)  # L2 flush between timed iterations (256 MiB > 126 MB L2), outside the timed events
+            torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        total_ms = sum(ms)
+        t = torch.tensor([total_ms, float(rays), trav_ms, float(trav_launches), float(launches), sum(bms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+            return dict(ms=mx[0].item(), rays=sm[1].item(), trav_ms=mx[2].item(), trav_launches=t[3].item(), launches=sm[4].item(), build_ms=mx[5].item() / steps)
+        return dict(ms=total_ms, rays=float(rays), trav_ms=trav_ms, trav_launches=float(trav_launches), launches=float(launches), build_ms=sum(bms) / steps)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dev_res = timed(step_device, a.steps, a.warmup)
+    sampler.stop_flag = True
+    e2e_res = timed(step_host, a.steps, max(1, a.warmup - 1))
+
+    # algorithmic bytes of the dominant kernel (traverse_kernel): one instrumented frame, same frame data
+    cnt = api.Counters()
+    fr = frames_d[a.warmup % nframes]
+    sc.update_triangles(fr[0], fr[1], fr[2]); sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+    sc.render_device(W, Hh, spp, img_d, flags=(rflags & ~api.TIME_TRAVERSE) | api.COUNTERS, tiles=tiles, counters=cnt)
+    torch.cuda.synchronize()
+    alg = torch.tensor([64.0 * cnt.nodes_visited + 48.0 * cnt.leaf_tests, float(cnt.nodes_visited), float(cnt.leaf_tests), float(cnt.rays)],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(alg, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    # per-launch figures: algorithmic bytes of one frame / traverse launches of one frame; duration = live CUDA-event average
+    launches_per_frame = dev_res["trav_launches"] / a.steps
+    bytes_per_launch = alg[0].item() / world / max(launches_per_frame, 1)   # per rank, like the per-rank event time
+    ms_per_launch = dev_res["trav_ms"] / max(dev_res["trav_launches"], 1)
+    achieved = bytes_per_launch / (ms_per_launch * 1e-3) / 1e9 if ms_per_launch > 0 else 0.0
+    value = dev_res["rays"] / (dev_res["ms"] * 1e-3) / 1e6
+    e2e = e2e_res["rays"] / (e2e_res["ms"] * 1e-3) / 1e6
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": dev_res["ms"] / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": workload_name(a), "lane": "near-first" if a.near_first else "reference-order (bit-exact)",
+                   "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
+                   "parallelism": "scene replicated, image in interleaved 32x8 tiles over %d GPU(s), NCCL broadcast + framebuffer reduce" % world},
+        "lbvh_build_ms": dev_res["build_ms"],
+        "rays_per_step": dev_res["rays"] / a.steps,
+        "nodes_per_ray": alg[1].item() / max(alg[3].item(), 1), "leaf_tests_per_ray": alg[2].item() / max(alg[3].item(), 1),
+        "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 3 * 12 * n * world, "d2h_bytes_per_step": W * Hh * 4,
+                "ms_per_step": e2e_res["ms"] / a.steps},
+        "gpu_launches": int(dev_res["launches"]),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "traverse_kernel", "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                     "bytes_per_launch": bytes_per_launch, "ms_per_launch": ms_per_launch,
+                     "share_of_step": dev_res["trav_ms"] / dev_res["ms"],
+                     "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test; node and triangle arrays (64+48 MB) are mostly L2 hits, so achieved may exceed the HBM peak"},
+        "clocks": sampler.summary(),
+    }
+    if not a.no_cpu_baseline and world == 1:
+        try:
+            line["cpu_baseline"] = cpu_baseline(a, cfg, {"tri": [p0, p1, p2], "tri_mat": arrays["tri_mat"].cpu().numpy(),
+                                                       "refs": arrays["refs"].cpu().numpy(), "suns": arrays["suns"]})
+        except Exception as e:  # the baseline is a reported figure, never the product path
+            line["cpu_baseline"] = {"error": repr(e)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

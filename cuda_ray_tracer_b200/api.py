@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200rt.so")
 
 BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN = 0, 1, 2
-SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS = 0, 1, 2, 4, 8
+SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE = 0, 1, 2, 4, 8, 16
 
 
 class RtError(RuntimeError):
@@ -49,7 +49,7 @@ class TileSet(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("nodes_visited", C.c_uint64), ("leaf_tests", C.c_uint64),
                 ("shaded_hits", C.c_uint64), ("wavefront_iters", C.c_uint32), ("passes", C.c_uint32), ("render_ms", C.c_float),
-                ("kernel_launches", C.c_uint32), ("traverse_ms", C.c_float)]
+                ("kernel_launches", C.c_uint32), ("traverse_ms", C.c_float), ("traverse_launches", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -240,6 +240,11 @@ class Scene:
         _check(load_library().rt_render_host(self.h, w, h, aa, flags, C.byref(tiles) if tiles else None, _ptr(rgba), _ptr(ids), _ptr(wr),
                                              C.byref(cnt)), "rt_render_host")
         return dict(rgba=rgba, ids=ids, written=wr, counters=cnt)
+
+    def render_host_into(self, rgba, w, h, aa, flags=SPP_REF, tiles=None, counters=None):
+        """rt_render_host into a caller-owned host buffer (numpy array or pinned torch tensor, [h][w][4] u8)"""
+        _check(load_library().rt_render_host(self.h, w, h, aa, flags, C.byref(tiles) if tiles else None, _ptr(rgba), None, None,
+                                             C.byref(counters) if counters is not None else None), "rt_render_host")
 
     # same with caller-owned device buffers (torch tensors / raw pointers), asynchronous on `stream`
     def render_device(self, w, h, aa, d_rgba, flags=SPP_REF, tiles=None, d_ids=None, d_written=None, counters=None, stream=None):

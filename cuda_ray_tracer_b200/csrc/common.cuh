@@ -88,6 +88,7 @@ struct rt_scene {
   int root = 0;
   bool built = false; int built_bits = 0; bool built_topdown = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float* upd_stage[3] = {nullptr, nullptr, nullptr};  // device staging of host vertex arrays (rt_scene_update_triangles)
   // render state (allocated lazily, reused)
   void* rstate = nullptr;
 };

@@ -752,6 +752,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   P.ref_order = (flags & RT_TRAVERSE_NEAR_FIRST) ? 0 : 1;
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;
+  const bool time_trav = (flags & (RT_COUNTERS | RT_TIME_TRAVERSE)) != 0;
   const bool both = s->any_shiny && s->any_trans;
   const int gi = s->cfg.gi != 0 ? 1 : 0;
   P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
@@ -822,16 +823,16 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     while (n_in > 0) {
       iters++; rays += n_in;
       RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
-      if (count) RT_CUDA(cudaEventRecord(rs->t0, st));
+      if (time_trav) RT_CUDA(cudaEventRecord(rs->t0, st));
       const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n_in + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
       launch_traverse(P.ref_order != 0, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats);
-      if (count) RT_CUDA(cudaEventRecord(rs->t1, st));
+      if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
       shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
       launches += 2;
       RT_CUDA(cudaGetLastError());
       RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 8, cudaMemcpyDeviceToHost, st));
       RT_CUDA(cudaStreamSynchronize(st));
-      if (count) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
+      if (time_trav) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
       n_in = rs->h_count[0];
       if (rs->h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
       std::swap(qin, qout);
@@ -845,7 +846,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (counters) {
     memset(counters, 0, sizeof(*counters));
     counters->rays = rays; counters->samples = samples; counters->wavefront_iters = iters; counters->passes = passes;
-    counters->kernel_launches = launches; counters->traverse_ms = trav_ms;
+    counters->kernel_launches = launches; counters->traverse_ms = trav_ms; counters->traverse_launches = iters;
     RT_CUDA(cudaEventElapsedTime(&counters->render_ms, rs->e0, rs->e1));
     unsigned long long hs[3];
     RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
@@ -905,7 +906,7 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   if (counters) {
     RT_CUDA(cudaStreamSynchronize(st));
     memset(counters, 0, sizeof(*counters));
-    counters->rays = (uint64_t)n; counters->kernel_launches = 3;
+    counters->rays = (uint64_t)n; counters->kernel_launches = 3; counters->traverse_launches = 1;
     RT_CUDA(cudaEventElapsedTime(&counters->traverse_ms, rs->e0, rs->e1));
     counters->render_ms = counters->traverse_ms;
     unsigned long long hs[3];

@@ -216,6 +216,7 @@ extern "C" int rt_scene_destroy(rt_scene* s) {
   rt_render_free_state(s);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
+  for (int k = 0; k < 3; k++) cudaFree(s->upd_stage[k]);
   cudaFree(s->arena);
   delete s;
   return RT_OK;
@@ -228,22 +229,20 @@ extern "C" int rt_scene_update_triangles(rt_scene* s, const float* p0, const flo
   cudaStream_t st = (cudaStream_t)stream;
   const float* src[3] = {p0, p1, p2};
   const float* dev[3];
-  void* tmp[3] = {nullptr, nullptr, nullptr};
+  bool staged = false;
   for (int k = 0; k < 3; k++) {
     cudaPointerAttributes at;
     cudaError_t e = cudaPointerGetAttributes(&at, src[k]);
     if (e == cudaSuccess && at.type == cudaMemoryTypeDevice) { dev[k] = src[k]; continue; }
     cudaGetLastError();
-    RT_CUDA(cudaMalloc(&tmp[k], (size_t)s->nt * 12));
-    RT_CUDA(cudaMemcpyAsync(tmp[k], src[k], (size_t)s->nt * 12, cudaMemcpyDefault, st));
-    dev[k] = (const float*)tmp[k];
+    if (!s->upd_stage[k]) RT_CUDA(cudaMalloc((void**)&s->upd_stage[k], (size_t)s->nt * 12));  // kept for the next frame
+    RT_CUDA(cudaMemcpyAsync(s->upd_stage[k], src[k], (size_t)s->nt * 12, cudaMemcpyDefault, st));
+    dev[k] = s->upd_stage[k];
+    staged = true;
   }
   update_tris_kernel<<<(s->nt + 255) / 256, 256, 0, st>>>(s->nt, dev[0], dev[1], dev[2], s->tri_prim, s->prim_bv, s->prim_tv);
   RT_CUDA(cudaGetLastError());
   s->built = false;
-  if (tmp[0] || tmp[1] || tmp[2]) {
-    RT_CUDA(cudaStreamSynchronize(st));
-    for (int k = 0; k < 3; k++) if (tmp[k]) cudaFree(tmp[k]);
-  }
+  (void)staged;
   return RT_OK;
 }

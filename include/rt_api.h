@@ -98,7 +98,8 @@ enum {
                                  order, which only the default order reproduces      */
   RT_ROUGH_ZYX        = 4u,   /* draw order of the three unsequenced standerdD() arguments
                                  (draw.cu:335-337): z,y,x instead of x,y,z                          */
-  RT_COUNTERS         = 8u    /* fill node/leaf counters (slower kernels)                          */
+  RT_COUNTERS         = 8u,   /* fill node/leaf counters (slower kernels) and traverse_ms          */
+  RT_TIME_TRAVERSE    = 16u   /* fill traverse_ms (CUDA events around the traverse launches) only  */
 };
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
   int32_t tile_w, tile_h, num_ranks, rank;
@@ -112,7 +113,8 @@ typedef struct rt_counters {
   uint32_t wavefront_iters, passes;
   float    render_ms;       /* device time generate..resolve                                        */
   uint32_t kernel_launches; /* kernels launched by this call                                        */
-  float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS)                    */
+  float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS / RT_TIME_TRAVERSE) */
+  uint32_t traverse_launches;
 } rt_counters;
 int rt_render(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
               uint8_t* d_rgba, int32_t* d_hit_id, uint8_t* d_written, rt_counters* counters, void* stream);

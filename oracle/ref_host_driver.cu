@@ -66,6 +66,35 @@ ref_scene* ref_load(const char* path) {
 }
 void ref_free(ref_scene* r) { delete r; }
 
+// Programmatic scenes (synthetic soups for bench.py --impl reference): the same host objects parse.cpp
+// builds for `xyz`/`tri`/`sphere`/`sun` lines (src/parse.cpp:130-216), made with the reference's own
+// constructors (Triangle(Vertex,Vertex,Vertex,RGB): include/object.cuh:165-191), without the text detour.
+ref_scene* ref_new(int width, int height, int bounces, int aa, const float* eye3, const float* forward3) {
+  ref_scene* r = new ref_scene();
+  StlConfig& s = r->stl;
+  s.width = width; s.height = height; s.bounces = bounces; s.aa = aa;
+  s.eye = point3(eye3[0], eye3[1], eye3[2]);
+  s.forward = vec3(forward3[0], forward3[1], forward3[2]);   // parse.cpp:61-65
+  s.right = cross(s.forward, s.up).normalize();
+  s.up = cross(s.right, s.forward).normalize();
+  return r;
+}
+void ref_add_triangles(ref_scene* r, int n, const float* p0, const float* p1, const float* p2, const float* mat11) {
+  StlConfig& s = r->stl;
+  for (int i = 0; i < n; i++) {
+    const float* m = mat11 + 11 * (size_t)i;
+    Triangle t(Vertex(p0[3 * i], p0[3 * i + 1], p0[3 * i + 2]), Vertex(p1[3 * i], p1[3 * i + 1], p1[3 * i + 2]),
+               Vertex(p2[3 * i], p2[3 * i + 1], p2[3 * i + 2]), RGB(m[0], m[1], m[2]));
+    t.mat.shininess = RGB(m[3], m[4], m[5]); t.mat.trans = RGB(m[6], m[7], m[8]); t.mat.ior = m[9]; t.mat.roughness = m[10];
+    s.host_triangles_data.push_back(t);
+    s.host_primitive_references.push_back(PrimitiveReference(PrimitiveType::TRIANGLE, (unsigned)s.host_triangles_data.size() - 1));
+  }
+}
+void ref_add_sun(ref_scene* r, const float* dir3, const float* color3) {
+  r->stl.sun_data.push_back(Sun(dir3[0], dir3[1], dir3[2], RGB(color3[0], color3[1], color3[2])));
+}
+void ref_finish(ref_scene* r) { fill_raw(r); }
+
 void ref_counts(ref_scene* r, int* out6) {
   out6[0] = r->rc.num_spheres; out6[1] = r->rc.num_triangles; out6[2] = r->rc.num_total_primitives;
   out6[3] = r->rc.num_sun; out6[4] = r->rc.num_bulbs; out6[5] = r->rc.num_planes;

@@ -22,6 +22,10 @@ def lib():
         vp, fp = C.c_void_p, C.POINTER(C.c_float)
         L.ref_load.restype = vp; L.ref_load.argtypes = [C.c_char_p]
         L.ref_free.argtypes = [vp]
+        L.ref_new.restype = vp; L.ref_new.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+        L.ref_add_triangles.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+        L.ref_add_sun.argtypes = [vp, vp, vp]
+        L.ref_finish.argtypes = [vp]
         L.ref_counts.argtypes = [vp, C.POINTER(C.c_int)]
         L.ref_config.argtypes = [vp, C.POINTER(C.c_int), fp]
         L.ref_tri.restype = fp; L.ref_tri.argtypes = [vp, C.c_int]
@@ -38,8 +42,8 @@ def lib():
 
 
 class RefScene:
-    def __init__(self, path):
-        self.h = C.c_void_p(lib().ref_load(path.encode()))
+    def __init__(self, path=None, handle=None):
+        self.h = C.c_void_p(lib().ref_load(path.encode())) if handle is None else handle
         c = (C.c_int * 6)(); lib().ref_counts(self.h, c)
         self.n = dict(zip(("spheres", "triangles", "prims", "suns", "bulbs", "planes"), list(c)))
 
@@ -87,6 +91,21 @@ class RefScene:
         ids = np.zeros(len(org), np.int32); ts = np.zeros(len(org), np.float32)
         lib().ref_trace_ids(self.h, len(org), _p(org), _p(dirs), _p(ids), _p(ts))
         return ids, ts
+
+
+def scene_from_arrays(cfg, arrays):
+    """triangle-only synthetic scene built with the reference's own constructors (bench.py --impl reference)"""
+    L = lib()
+    eye = np.asarray(cfg["eye"], np.float32); fwd = np.asarray(cfg["forward"], np.float32)
+    h = C.c_void_p(L.ref_new(int(cfg["width"]), int(cfg["height"]), int(cfg["bounces"]), int(cfg["aa"]), _p(eye), _p(fwd)))
+    t = arrays["tri"]; m = np.ascontiguousarray(arrays["tri_mat"], np.float32)
+    p0, p1, p2 = [np.ascontiguousarray(a, np.float32) for a in t[:3]]
+    L.ref_add_triangles(h, len(p0), _p(p0), _p(p1), _p(p2), _p(m))
+    for s in arrays.get("suns", []):
+        s = np.asarray(s, np.float32)
+        L.ref_add_sun(h, _p(s[:3].copy()), _p(s[3:].copy()))
+    L.ref_finish(h)
+    return RefScene(handle=h)
 
 
 def curand(seed, subseq, n):
