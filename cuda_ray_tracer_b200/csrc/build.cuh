@@ -47,5 +47,42 @@ __device__ inline RtBox rt_prim_box(float4 a, float4 b, float4 c) {
   return o;
 }
 
+// Leaf slack: how far outside its leaf AABB a hit point the reference's primitive test ACCEPTS can lie.
+// The triangle test tolerates barycentrics down to -1e-3 (src/struct.cu:150-152, EPSILON), so accepted
+// points fill a slightly larger triangle than the one the AABB was built from (include/interval.cuh:61-81);
+// a sphere hit near a silhouette carries the cancellation error of sqrt(r^2 - d^2) (struct.cu:88-98).  The
+// traversal uses the slack (max over the subtree, stored in the node half's aux word) to cull by distance
+// only when no acceptable hit inside the subtree can be closer — see traverse.cuh, exact near-first lane.
+// Evaluated in double from the float e1/e2 actually used by the test, so slivers with inaccurate
+// e1/e2 get the (large) slack they need; anything non-finite or ill-conditioned gets +INF (never culled).
+__device__ inline float rt_leaf_slack(float4 a, float4 b, float4 c, float4 t0, float4 t1, float4 t2, const RtBox& box) {
+  if (c.w == RT_TAG_SPHERE) return 2e-3f * fabsf(a.w);
+  const double p0[3] = {a.x, a.y, a.z}, p1[3] = {a.w, b.x, b.y}, p2[3] = {b.z, b.w, c.x};
+  const double nor[3] = {t0.w, t1.x, t1.y}, e1[3] = {t1.z, t1.w, t2.x}, e2[3] = {t2.y, t2.z, t2.w};
+  if (nor[0] == 0.0 && nor[1] == 0.0 && nor[2] == 0.0) return 0.f;  // den == 0 for every ray: never hit
+  double d1[3], d2[3], g11 = 0, g12 = 0, g21 = 0, g22 = 0, ne1 = 0, ne2 = 0, nd = 0;
+  for (int k = 0; k < 3; k++) {
+    d1[k] = p1[k] - p0[k]; d2[k] = p2[k] - p0[k];
+    g11 += e1[k] * d1[k]; g12 += e1[k] * d2[k]; g21 += e2[k] * d1[k]; g22 += e2[k] * d2[k];
+    ne1 += fabs(e1[k]); ne2 += fabs(e2[k]); nd += fabs(d1[k]) + fabs(d2[k]);
+  }
+  const double det = g11 * g22 - g12 * g21;
+  if (!(fabs(det) > 1e-3) || !(fabs(det) < 1e3) || !isfinite(ne1 + ne2 + nd)) return INFINITY;
+  // tolerance on the barycentrics: EPSILON, plus the rounding of the float dot products that compute them
+  const double eps = 0.001 * 1.01 + 1e-5 + 4e-6 * (ne1 + ne2) * nd;
+  const double lo[3] = {box.xmin, box.ymin, box.zmin}, hi[3] = {box.xmax, box.ymax, box.zmax};
+  const double cb[3][2] = {{-eps, -eps}, {1.0 + 2.0 * eps, -eps}, {-eps, 1.0 + 2.0 * eps}};
+  double slack = 0.0;
+  for (int q = 0; q < 3; q++) {
+    const double al = (g22 * cb[q][0] - g12 * cb[q][1]) / det, be = (-g21 * cb[q][0] + g11 * cb[q][1]) / det;
+    for (int k = 0; k < 3; k++) {
+      const double x = p0[k] + al * d1[k] + be * d2[k];
+      slack = fmax(slack, fmax(lo[k] - x, x - hi[k]));
+    }
+  }
+  if (!isfinite(slack)) return INFINITY;
+  return (float)(slack * 1.02) * 1.0001f + 1e-30f;
+}
+
 // build_sort.cu
 int rt_build_codes_and_sort(rt_scene* s, int morton_bits, unsigned flags, cudaStream_t st, uint32_t* launches);

@@ -37,15 +37,17 @@ struct Delta {
   }
 };
 
-__device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref) {
+// aux = hit slack of the subtree (build.cuh, rt_leaf_slack)
+__device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref, float slack) {
   float4* h = nodes + 4 * (size_t)slot + 2 * side;
   __stcg(h, make_float4(b.xmin, b.ymin, b.zmin, b.xmax));
-  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), 0.f));
+  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), slack));
 }
-__device__ inline void load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
+__device__ inline float load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
   const float4* h = nodes + 4 * (size_t)slot + 2 * side;
   float4 u = __ldcg(h), v = __ldcg(h + 1);
   b.xmin = u.x; b.ymin = u.y; b.zmin = u.z; b.xmax = u.w; b.ymax = v.x; b.zmax = v.y;
+  return v.w;
 }
 __device__ inline RtBox union_box(const RtBox& l, const RtBox& r) {  // AABB(left,right), interval.cuh:83-88
   RtBox o;
@@ -66,10 +68,10 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   const uint32_t p = perm[k];
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
   // gather the trace view into Morton order (leaf k <-> record k)
-  sorted_tv[3 * (size_t)k] = __ldg(tv + 3 * (size_t)p);
-  sorted_tv[3 * (size_t)k + 1] = __ldg(tv + 3 * (size_t)p + 1);
-  sorted_tv[3 * (size_t)k + 2] = __ldg(tv + 3 * (size_t)p + 2);
+  const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+  sorted_tv[3 * (size_t)k] = t0; sorted_tv[3 * (size_t)k + 1] = t1; sorted_tv[3 * (size_t)k + 2] = t2;
   RtBox box = rt_prim_box(a, b, c);
+  float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
   Delta<KeyT> D{keys, n};
   int l = k, r = k;
@@ -82,13 +84,13 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
     const int dl = D.adj(l - 1), dr = D.adj(r);
     int s, side, mine;
     if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
-    store_half(nodes, s, side, box, ref);
+    store_half(nodes, s, side, box, ref, slack);
     __threadfence();
     const int other = atomicExch(flags + s, mine);
     if (other == -1) return;  // sibling not there yet: it will finish this node
     __threadfence();
     RtBox sib;
-    load_half_box(nodes, s, side ^ 1, sib);
+    slack = fmaxf(slack, load_half_box(nodes, s, side ^ 1, sib));
     if (side == 0) { r = other; box = union_box(box, sib); } else { l = other; box = union_box(sib, box); }
     ref = (uint32_t)s;
   }
@@ -150,21 +152,21 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   if (k >= n) return;
   const uint32_t p = perm[k];
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
-  sorted_tv[3 * (size_t)k] = __ldg(tv + 3 * (size_t)p);
-  sorted_tv[3 * (size_t)k + 1] = __ldg(tv + 3 * (size_t)p + 1);
-  sorted_tv[3 * (size_t)k + 2] = __ldg(tv + 3 * (size_t)p + 2);
+  const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+  sorted_tv[3 * (size_t)k] = t0; sorted_tv[3 * (size_t)k + 1] = t1; sorted_tv[3 * (size_t)k + 2] = t2;
   RtBox box = rt_prim_box(a, b, c);
+  float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
   if (n == 1) { *root_out = (int)ref; root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax; return; }
   int pi = parent[n - 1 + k];
   while (true) {  // set_aabb_kernel_adapted, lbvh_builder.cu:353-386, plus the missing fences (F9)
     const int par = pi >> 1, side = pi & 1;
-    store_half(nodes, par, side, box, ref);
+    store_half(nodes, par, side, box, ref, slack);
     __threadfence();
     if (atomicExch(counters + par, 1) == -1) return;  // counters were initialised to -1
     __threadfence();
     RtBox sib;
-    load_half_box(nodes, par, side ^ 1, sib);
+    slack = fmaxf(slack, load_half_box(nodes, par, side ^ 1, sib));
     box = side == 0 ? union_box(box, sib) : union_box(sib, box);
     ref = (uint32_t)par;
     pi = parent[par];

@@ -7,7 +7,7 @@
 //   --bounds shipped|computed   Morton bounds: the reference as shipped (+INF/-INF, every code 0,
 //                               SURVEY F1) or the box parse.cpp accumulates and drops (default)
 //   --spp ref|true              aa>=2 sample semantics; default ref
-//   --near-first                nearer-child-first traversal (faster; see RT_TRAVERSE_NEAR_FIRST)
+//   --near-first | --ref-order  traversal lane (RT_TRAVERSE_NEAR_FIRST / RT_TRAVERSE_REF_ORDER); default: exact near-first
 //   --bits 30|63                Morton code width
 //   --device N, --counters, --ids FILE (raw int32 hit ids), --repeat N
 #include <chrono>
@@ -27,7 +27,7 @@ static void die(const char* what) {  // CUDA_CHECK → exit(EXIT_FAILURE), main.
 }
 
 int main(int argc, char* argv[]) {
-  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds shipped|computed] [--spp ref|true] [--near-first] [--bits 30|63] [--device N] [--counters] [--ids FILE] [--repeat N]\n", argv[0]); return 1; }
+  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds shipped|computed] [--spp ref|true] [--near-first|--ref-order] [--bits 30|63] [--device N] [--counters] [--ids FILE] [--repeat N]\n", argv[0]); return 1; }
   unsigned bflags = RT_BOUNDS_COMPUTED, rflags = RT_SPP_REF;
   int bits = 30, device = 0, repeat = 1; bool counters = false; std::string ids_path;
   for (int i = 2; i < argc; i++) {
@@ -35,6 +35,7 @@ int main(int argc, char* argv[]) {
     if (a == "--bounds" && i + 1 < argc) bflags = strcmp(argv[++i], "shipped") == 0 ? RT_BOUNDS_FROM_DESC : RT_BOUNDS_COMPUTED;
     else if (a == "--spp" && i + 1 < argc) { if (strcmp(argv[++i], "true") == 0) rflags |= RT_SPP_TRUE; }
     else if (a == "--near-first") rflags |= RT_TRAVERSE_NEAR_FIRST;
+    else if (a == "--ref-order") rflags |= RT_TRAVERSE_REF_ORDER;
     else if (a == "--bits" && i + 1 < argc) bits = atoi(argv[++i]);
     else if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
     else if (a == "--counters") { counters = true; rflags |= RT_COUNTERS; }

@@ -40,7 +40,7 @@ struct RenderParams {
   int tile_w, tile_h, tiles_x, num_ranks, rank, slots_per_tile;
   int slot0, npix, S;   // this pass: pixel slots [slot0, slot0+npix), S = npix * spp samples
   int depth;        // continuation stack depth (frames per sample)
-  int ref_order, rough_zyx, need_rng;
+  int ref_order /* traversal lane, RT_LANE_* */, rough_zyx, need_rng;
   int num_lights;
 };
 
@@ -639,7 +639,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
     RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
     int per_sm = 0, sms = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_kernel<false, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_kernel<RT_LANE_EXACT, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
     if (per_sm < 1) per_sm = 1;
     st->trav_grid = sms * per_sm;  // persistent grid: every SM full, 148 x resident CTAs on B200
@@ -663,10 +663,16 @@ RtDeviceScene device_scene(const rt_scene* s) {
   return d;
 }
 
+int lane_of(unsigned flags) {
+  return (flags & RT_TRAVERSE_REF_ORDER) ? RT_LANE_REF : (flags & RT_TRAVERSE_NEAR_FIRST) ? RT_LANE_NEAR : RT_LANE_EXACT;
+}
 template <typename... Args>
-void launch_traverse(bool ref_order, bool count, int grid, cudaStream_t st, Args... args) {
-  if (ref_order) { if (count) traverse_kernel<true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); }
-  else { if (count) traverse_kernel<false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); }
+void launch_traverse(int lane, bool count, int grid, cudaStream_t st, Args... args) {
+#define RT_LAUNCH(L) do { if (count) traverse_kernel<L, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<L, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); } while (0)
+  if (lane == RT_LANE_REF) RT_LAUNCH(RT_LANE_REF);
+  else if (lane == RT_LANE_NEAR) RT_LAUNCH(RT_LANE_NEAR);
+  else RT_LAUNCH(RT_LANE_EXACT);
+#undef RT_LAUNCH
 }
 
 int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
@@ -749,7 +755,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   P.slots_per_tile = P.tile_w * P.tile_h;
   long long nslots = owned * P.slots_per_tile;
   if (!tiles) nslots = P.covered;  // one tile = the image: slot == pixel
-  P.ref_order = (flags & RT_TRAVERSE_NEAR_FIRST) ? 0 : 1;
+  P.ref_order = lane_of(flags);
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;
   const bool time_trav = (flags & (RT_COUNTERS | RT_TIME_TRAVERSE)) != 0;
@@ -825,7 +831,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t0, st));
       const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n_in + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-      launch_traverse(P.ref_order != 0, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats);
+      launch_traverse(P.ref_order, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats);
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
       shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
       launches += 2;
@@ -899,7 +905,7 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
   RT_CUDA(cudaEventRecord(rs->e0, st));
   const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-  launch_traverse((flags & RT_TRAVERSE_NEAR_FIRST) == 0, count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats);
+  launch_traverse(lane_of(flags), count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats);
   RT_CUDA(cudaEventRecord(rs->e1, st));
   unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(rs->trace_hits, s->sorted_perm, n, d_hit_id, d_hit_t);
   RT_CUDA(cudaGetLastError());

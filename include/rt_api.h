@@ -90,16 +90,20 @@ enum {
   RT_SPP_REF          = 0u,   /* aa<=1: render_kernel; aa>=2: 32 samples/pixel over the reference's
                                  launch shape (draw.cu:135-213,226-238)                 */
   RT_SPP_TRUE         = 1u,   /* aa>=2: exactly aa samples for every pixel, seed (1234+pixel, s)   */
-  RT_TRAVERSE_NEAR_FIRST = 2u, /* nearer child first + distance-sorted stack culling instead of the
-                                 reference's left-first order (bvh_traversal.cu:149-179).  Same hit
-                                 whenever every hit point lies inside its own AABBs; the triangle
-                                 test's -1e-3 barycentric tolerance (struct.cu:150-152) lets a hit sit
-                                 just outside, and then the reference's answer depends on its visiting
-                                 order, which only the default order reproduces      */
+  RT_TRAVERSE_NEAR_FIRST = 2u, /* plain nearer-child-first traversal with distance culling.  Same hit as
+                                 the reference whenever every hit point lies inside its own AABBs; the
+                                 triangle test's -1e-3 barycentric tolerance (struct.cu:150-152) lets a
+                                 hit sit just outside, and then the reference's answer depends on its
+                                 visiting order.  The DEFAULT lane is also near-first but provably returns
+                                 the reference's answer (slack-inflated culling + per-ray certificate +
+                                 reference-order fallback); this flag only removes that
+                                 machinery, to measure what exactness costs                          */
   RT_ROUGH_ZYX        = 4u,   /* draw order of the three unsequenced standerdD() arguments
                                  (draw.cu:335-337): z,y,x instead of x,y,z                          */
   RT_COUNTERS         = 8u,   /* fill node/leaf counters (slower kernels) and traverse_ms          */
-  RT_TIME_TRAVERSE    = 16u   /* fill traverse_ms (CUDA events around the traverse launches) only  */
+  RT_TIME_TRAVERSE    = 16u,  /* fill traverse_ms (CUDA events around the traverse launches) only  */
+  RT_TRAVERSE_REF_ORDER = 32u /* every ray in the reference's left-first visiting order
+                                 (bvh_traversal.cu:149-179): the exact lane's fallback, for all rays */
 };
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
   int32_t tile_w, tile_h, num_ranks, rank;

@@ -53,7 +53,7 @@ def check_trace(gi, gt, ids, ts, flags):
         assert np.array_equal(gt.view(np.uint32), ts.view(np.uint32)), "hit distances differ"
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
 @pytest.mark.parametrize("mode", [O.BOUNDS_COMPUTED, O.BOUNDS_SHIPPED])
 def test_trace_ids_mixed_scene(flags, mode):
     cfg, a = H.mixed_scene(3000)
@@ -68,7 +68,7 @@ def test_trace_ids_mixed_scene(flags, mode):
 
 
 @pytest.mark.parametrize("name", ["tri", "redchair", "tenthousand", "spiral"])
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
 def test_trace_ids_scene_files(name, flags):
     p = H.scene_path(name)
     if p is None:
@@ -89,7 +89,7 @@ def test_ref_order_node_counts_match_oracle():
     sc = built_pair(o)
     org, d = random_rays(5000, 3)
     ids, ts, oc = o.trace(org, d)
-    gi, gt, cnt = gpu_trace(sc, org, d, api.COUNTERS)
+    gi, gt, cnt = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER | api.COUNTERS)
     assert np.array_equal(gi, ids)
     assert cnt.leaf_tests == oc.leaf_tests
     assert cnt.nodes_visited + cnt.leaf_tests == oc.nodes_visited  # the oracle counts leaf visits as node visits
@@ -120,7 +120,7 @@ def compare_render(o, sc, w, h, aa, spp_mode=O.SPP_REF, flags=0, tol=1, frac_ok=
     return g, r
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
 def test_render_tri_scene(flags):
     p = H.scene_path("tri")
     if p is None:
@@ -166,7 +166,7 @@ def synthetic_full_featured(n=4000, seed=11, rough=0.0):
     return cfg, a
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
 def test_render_all_shading_paths(flags):
     cfg, a = synthetic_full_featured()
     o = H.oracle_from_arrays(cfg, a)
@@ -264,3 +264,69 @@ def test_planes_only_scene():
     g = sc.render(40, 30, 0, want_ids=True)
     assert np.array_equal(g["ids"], r["ids"]) and (g["ids"] == -2).any()
     assert np.abs(g["rgba"].astype(int) - r["rgba"].astype(int)).max() <= 1
+
+
+def sliver_scene(n=6000, seed=21):
+    """needle and sliver triangles (inaccurate e1/e2), duplicated vertices, shared edges, coplanar fans: the
+    geometry where accepted hits lie outside their own AABBs most often"""
+    rng = np.random.RandomState(seed)
+    c = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+    u = rng.uniform(-0.3, 0.3, (n, 3)).astype(np.float32)
+    kind = rng.randint(0, 4, n)
+    v = rng.uniform(-0.3, 0.3, (n, 3)).astype(np.float32)
+    v[kind == 0] = (u[kind == 0] * (1 + 1e-4)) + rng.uniform(-1e-5, 1e-5, ((kind == 0).sum(), 3))   # slivers
+    v[kind == 1] = u[kind == 1] * np.float32(1e-3)                                                 # needles
+    p0, p1, p2 = c, (c + u).astype(np.float32), (c + v).astype(np.float32)
+    m = (kind == 2)                                                                                 # axis-aligned fans sharing edges
+    p0[m, 2] = np.round(p0[m, 2] * 4) / 4; p1[m, 2] = p0[m, 2]; p2[m, 2] = p0[m, 2]
+    p0[m, :2] = np.round(p0[m, :2] * 8) / 8; p1[m, :2] = p0[m, :2] + np.float32([0.125, 0]); p2[m, :2] = p0[m, :2] + np.float32([0, 0.125])
+    cfg = synth.default_config(64, 64, 0, eye=(0, 0, 3.5))
+    mat = np.zeros((n, 11), np.float32); mat[:, :3] = rng.uniform(0.2, 1, (n, 3)); mat[:, 9] = 1.458
+    a = dict(tri=[p0.copy(), p1.copy(), p2.copy(), None, None, None], tri_mat=mat,
+             refs=np.stack([np.ones(n, np.int32), np.arange(n, dtype=np.int32)], 1), suns=np.array([[1, 1, 1, 1, 1, 1]], np.float32),
+             bulbs=np.array([[0.2, 0.5, 2.0, 2, 2, 2]], np.float32))
+    return cfg, synth.finish_triangles(a)
+
+
+def test_exact_lane_equals_reference_order_on_slivers():
+    cfg, a = sliver_scene()
+    o = H.oracle_from_arrays(cfg, a)
+    sc = built_pair(o)
+    org, d = random_rays(400000, 5, 2.5)
+    # rays along the axes and inside the planes of the fans (grazing): the worst case for box/hit consistency
+    d[:50000] = np.float32([0, 0, -1]); org[:50000, 2] = 3
+    org[50000:100000, 2] = np.round(org[50000:100000, 2] * 4) / 4; d[50000:100000, 2] = 0
+    d[50000:100000] /= np.maximum(np.linalg.norm(d[50000:100000], axis=1, keepdims=True), 1e-9)
+    d = np.ascontiguousarray(d, np.float32)
+    ri, rt_, _ = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER)
+    ei, et, _ = gpu_trace(sc, org, d, 0)
+    assert np.array_equal(ei, ri) and np.array_equal(et.view(np.uint32), rt_.view(np.uint32)), "%d rays differ" % (ei != ri).sum()
+    oi, ot, _ = o.trace(org[:60000], d[:60000])
+    assert np.array_equal(ei[:60000], oi) and np.array_equal(et[:60000].view(np.uint32), ot.view(np.uint32))
+    # shading with sun + bulb shadow rays
+    a0 = sc.render(200, 150, 0, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(200, 150, 0, 0, want_ids=True)
+    assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"])
+
+
+def test_exact_lane_equals_reference_order_redchair_and_soup():
+    p = H.scene_path("redchair")
+    if p is not None:
+        o = O.OracleScene(p)
+        sc = built_pair(o)
+        for aa, (w, h) in ((0, (512, 512)), (32, (96, 96))):
+            a0 = sc.render(w, h, aa, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(w, h, aa, 0, want_ids=True)
+            assert np.array_equal(a0["ids"], a1["ids"]), "%d ids differ" % (a0["ids"] != a1["ids"]).sum()
+            assert np.array_equal(a0["rgba"], a1["rgba"]) and a0["counters"].rays == a1["counters"].rays
+    cfg, a = synth.soup(1_000_000, seed=1, width=64, height=64, aa=0)
+    a = synth.finish_triangles(a)
+    o = H.oracle_from_arrays(cfg, a)
+    sc = H.gpu_scene_from_oracle(o, O.BOUNDS_COMPUTED)
+    sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+    org, d = random_rays(2_000_000, 9, 2.0)
+    ri, rt_, c0 = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER | api.COUNTERS)
+    ei, et, c1 = gpu_trace(sc, org, d, api.COUNTERS)
+    assert np.array_equal(ei, ri) and np.array_equal(et.view(np.uint32), rt_.view(np.uint32)), "%d rays differ" % (ei != ri).sum()
+    print("nodes/ray reference order %.1f, exact near-first %.1f" % (c0.nodes_visited / len(org), c1.nodes_visited / len(org)))
+    assert c1.nodes_visited < 0.6 * c0.nodes_visited
+    a0 = sc.render(640, 360, 0, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(640, 360, 0, 0, want_ids=True)
+    assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"])
