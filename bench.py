@@ -306,7 +306,7 @@ def run_b200(a):
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": dev_res["ms"] / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(a), "lane": "near-first" if a.near_first else "reference-order (bit-exact)",
+        "config": {"workload": workload_name(a), "lane": "near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)",
                    "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
                    "parallelism": "scene replicated, image in interleaved 32x8 tiles over %d GPU(s), NCCL broadcast + framebuffer reduce" % world},
         "lbvh_build_ms": dev_res["build_ms"],

@@ -37,11 +37,13 @@ struct Delta {
   }
 };
 
-// aux = hit slack of the subtree (build.cuh, rt_leaf_slack)
+// aux = hit slack of the subtree (build.cuh, rt_leaf_slack) + 4e-7 * largest |coordinate| of the box: the
+// amount by which the traversal inflates the box before it culls the subtree by distance (traverse.cuh)
 __device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref, float slack) {
   float4* h = nodes + 4 * (size_t)slot + 2 * side;
+  const float cmax = fmaxf(fmaxf(fmaxf(fabsf(b.xmin), fabsf(b.xmax)), fmaxf(fabsf(b.ymin), fabsf(b.ymax))), fmaxf(fabsf(b.zmin), fabsf(b.zmax)));
   __stcg(h, make_float4(b.xmin, b.ymin, b.zmin, b.xmax));
-  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), slack));
+  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), slack + 4e-7f * cmax));
 }
 __device__ inline float load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
   const float4* h = nodes + 4 * (size_t)slot + 2 * side;
@@ -69,7 +71,7 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
   // gather the trace view into Morton order (leaf k <-> record k)
   const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
-  sorted_tv[3 * (size_t)k] = t0; sorted_tv[3 * (size_t)k + 1] = t1; sorted_tv[3 * (size_t)k + 2] = t2;
+  { float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k; rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f); }
   RtBox box = rt_prim_box(a, b, c);
   float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
@@ -153,7 +155,7 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   const uint32_t p = perm[k];
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
   const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
-  sorted_tv[3 * (size_t)k] = t0; sorted_tv[3 * (size_t)k + 1] = t1; sorted_tv[3 * (size_t)k + 2] = t2;
+  { float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k; rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f); }
   RtBox box = rt_prim_box(a, b, c);
   float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;

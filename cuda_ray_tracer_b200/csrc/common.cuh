@@ -6,7 +6,8 @@
 //   prim_tv  [n][3] float4  "trace view", file order.   triangle: p0.xyz nor.x | nor.yz e1.xy | e1.z e2.xyz
 //                                                      sphere:   c.xyz r      | 0 ...
 //   prim_mat [n][3] float4  Materials (11 floats + pad), file order
-//   sorted_tv[n][3] float4  prim_tv gathered into Morton order (leaf k reads record k)
+//   sorted_tv[n][4] float4  prim_tv gathered into Morton order (leaf k reads record k), 64-byte records:
+//                            the three prim_tv words + (file-order index, 0, 0, 0)
 //   nodes    [n-1][4] float4 64-byte internal node = two 32-byte child halves
 //                            half: min.xyz max.x | max.yz ref aux      (ref<0: leaf, see below)
 // Everything the tracer touches is indexed by file-order primitive index or by sorted position;
@@ -19,6 +20,7 @@
 
 #include "../../include/rt_api.h"
 
+#define RT_TV_STRIDE 4  // float4 words per sorted leaf record
 #define RT_TAG_TRI 1.0f
 #define RT_TAG_SPHERE 2.0f
 

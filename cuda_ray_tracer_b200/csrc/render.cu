@@ -51,6 +51,7 @@ struct RenderBuffers {
   float4* frames;         // [(level*4 + q) * S + sample]
   float4 *qa, *qb;        // ray queues, 2 float4 per ray
   float2* hits;           // per queue slot
+  unsigned* fb_list;      // exact lane: rays to re-trace in reference order
   uint32_t* counters;     // [0] fetch ticket, [1] out-queue length, [2] overflow flag
   unsigned long long* stats;  // [0] nodes, [1] leaf tests, [2] shaded hits
   const uint32_t* rng_mats;   // power matrices P^m
@@ -223,14 +224,14 @@ __device__ __forceinline__ void reconstruct_hit(const RtDeviceScene& sc, int id,
   h.point = t * d + o;
   if (id >= 0) {
     const unsigned k = (unsigned)id & RT_LEAF_MASK;
-    const float4 a = __ldg(sc.sorted_tv + 3 * (size_t)k);
+    const float4 a = __ldg(sc.sorted_tv + RT_TV_STRIDE * (size_t)k);
     if ((unsigned)id & RT_SPHERE_BIT) {  // struct.cu:76-108
       const V3 c = mk3(a.x, a.y, a.z);
       const V3 cr0 = c - o;
       const bool inside = dot(cr0, cr0) < a.w * a.w;
       h.normal = normalize3(inside ? (c - h.point) : (h.point - c));
     } else {  // struct.cu:124,160
-      const float4 b = __ldg(sc.sorted_tv + 3 * (size_t)k + 1);
+      const float4 b = __ldg(sc.sorted_tv + RT_TV_STRIDE * (size_t)k + 1);
       const V3 nor = mk3(a.w, b.x, b.y);
       h.normal = (dot(d, nor) < 0.0f) ? nor : -nor;
     }
@@ -623,7 +624,7 @@ struct RenderState {
   cudaEvent_t e0 = nullptr, e1 = nullptr, t0 = nullptr, t1 = nullptr;
   int trav_grid = 0;
   uint8_t* d_rgba = nullptr; int32_t* d_ids = nullptr; uint8_t* d_written = nullptr; size_t img_px = 0;  // rt_render_host staging
-  float4* trace_q = nullptr; float2* trace_hits = nullptr; size_t trace_cap = 0;
+  float4* trace_q = nullptr; float2* trace_hits = nullptr; unsigned* trace_fb = nullptr; size_t trace_cap = 0;
 };
 
 RenderState* get_state(rt_scene* s) {
@@ -639,7 +640,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
     RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
     int per_sm = 0, sms = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_kernel<RT_LANE_EXACT, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
     if (per_sm < 1) per_sm = 1;
     st->trav_grid = sms * per_sm;  // persistent grid: every SM full, 148 x resident CTAs on B200
@@ -666,13 +667,23 @@ RtDeviceScene device_scene(const rt_scene* s) {
 int lane_of(unsigned flags) {
   return (flags & RT_TRAVERSE_REF_ORDER) ? RT_LANE_REF : (flags & RT_TRAVERSE_NEAR_FIRST) ? RT_LANE_NEAR : RT_LANE_EXACT;
 }
-template <typename... Args>
-void launch_traverse(int lane, bool count, int grid, cudaStream_t st, Args... args) {
-#define RT_LAUNCH(L) do { if (count) traverse_kernel<L, true><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); else traverse_kernel<L, false><<<grid, RT_TRAV_THREADS, 0, st>>>(args...); } while (0)
-  if (lane == RT_LANE_REF) RT_LAUNCH(RT_LANE_REF);
-  else if (lane == RT_LANE_NEAR) RT_LAUNCH(RT_LANE_NEAR);
-  else RT_LAUNCH(RT_LANE_EXACT);
-#undef RT_LAUNCH
+// one traversal of a ray queue: the lane's kernel, then (exact lane) the reference-order pass over the rays
+// whose certificate failed.  ctr: [0] fetch ticket, [3] fallback count, [4] fallback fetch ticket.
+void launch_traverse(int lane, bool count, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned n, float2* hits,
+                     unsigned* ctr, unsigned long long* stats, unsigned* fb_list) {
+  if (lane == RT_LANE_REF) {
+    if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, nullptr, nullptr);
+    else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, nullptr, nullptr);
+  } else if (lane == RT_LANE_NEAR) {
+    if (count) traverse_near_kernel<false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
+    else traverse_near_kernel<false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
+  } else {
+    if (count) traverse_near_kernel<true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
+    else traverse_near_kernel<true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
+    const int g2 = grid < 148 ? grid : 148;
+    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr + 4, stats, fb_list, ctr + 3);
+    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr + 4, stats, fb_list, ctr + 3);
+  }
 }
 
 int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
@@ -708,7 +719,7 @@ int rt_render_free_state(rt_scene* s) {
   if (!st) return RT_OK;
   cudaFree(st->pool); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
   cudaFree(st->rng.mats); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
-  cudaFree(st->trace_q); cudaFree(st->trace_hits);
+  cudaFree(st->trace_q); cudaFree(st->trace_hits); cudaFree(st->trace_fb);
   if (st->e0) { cudaEventDestroy(st->e0); cudaEventDestroy(st->e1); cudaEventDestroy(st->t0); cudaEventDestroy(st->t1); }
   delete st;
   s->rstate = nullptr;
@@ -772,7 +783,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   else if (P.need_rng) { rc = ensure_rng_tables(rs, 256, (int)((npx + 255) / 256)); if (rc) return rc; }
 
   // pass size: all per-sample state lives in one pool
-  const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8;
+  const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8 + 4;
   const size_t budget = env_size("RT_POOL_BYTES", (size_t)6 << 30);
   const long long total_samples = nslots * P.spp;
   long long max_s = (long long)(budget / per_sample);
@@ -782,7 +793,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (nslots == 0) npix_pass = 0;
   const size_t Smax = (size_t)npix_pass * P.spp;
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
-  const size_t need = al(Smax * 16) * 2 + al(Smax * 16) + al(Smax * 4) + al(Smax * 64 * P.depth) + al(Smax * 32) * 2 + al(Smax * 8) + 4096;
+  const size_t need = al(Smax * 16) * 2 + al(Smax * 16) + al(Smax * 4) + al(Smax * 64 * P.depth) + al(Smax * 32) * 2 + al(Smax * 8) + al(Smax * 4) + 4096;
   if (need > rs->pool_bytes) {
     if (rs->pool) cudaFree(rs->pool);
     rs->pool = nullptr; rs->pool_bytes = 0;
@@ -798,6 +809,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     B.frames = (float4*)p; p += al(Smax * 64 * P.depth);
     B.qa = (float4*)p; p += al(Smax * 32); B.qb = (float4*)p; p += al(Smax * 32);
     B.hits = (float2*)p; p += al(Smax * 8);
+    B.fb_list = (unsigned*)p; p += al(Smax * 4);
   }
   B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_base = rs->rng.base;
   const RtDeviceScene sc = device_scene(s);
@@ -828,10 +840,11 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     float4 *qin = B.qa, *qout = B.qb;
     while (n_in > 0) {
       iters++; rays += n_in;
-      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 20, st));
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t0, st));
       const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n_in + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-      launch_traverse(P.ref_order, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats);
+      launch_traverse(P.ref_order, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats, B.fb_list);
+      launches += P.ref_order == RT_LANE_EXACT ? 1 : 0;
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
       shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
       launches += 2;
@@ -894,18 +907,18 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   rc = fetch_root(s); if (rc) return rc;
   if (n == 0) return RT_OK;
   if ((size_t)n > rs->trace_cap) {
-    cudaFree(rs->trace_q); cudaFree(rs->trace_hits); rs->trace_q = nullptr; rs->trace_hits = nullptr; rs->trace_cap = 0;
-    RT_CUDA(cudaMalloc(&rs->trace_q, (size_t)n * 32)); RT_CUDA(cudaMalloc(&rs->trace_hits, (size_t)n * 8));
+    cudaFree(rs->trace_q); cudaFree(rs->trace_hits); cudaFree(rs->trace_fb); rs->trace_q = nullptr; rs->trace_hits = nullptr; rs->trace_fb = nullptr; rs->trace_cap = 0;
+    RT_CUDA(cudaMalloc(&rs->trace_q, (size_t)n * 32)); RT_CUDA(cudaMalloc(&rs->trace_hits, (size_t)n * 8)); RT_CUDA(cudaMalloc(&rs->trace_fb, (size_t)n * 4));
     rs->trace_cap = (size_t)n;
   }
   const bool count = (flags & RT_COUNTERS) != 0;
   const RtDeviceScene sc = device_scene(s);
-  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 20, st));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
   pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
   RT_CUDA(cudaEventRecord(rs->e0, st));
   const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-  launch_traverse(lane_of(flags), count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats);
+  launch_traverse(lane_of(flags), count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats, rs->trace_fb);
   RT_CUDA(cudaEventRecord(rs->e1, st));
   unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(rs->trace_hits, s->sorted_perm, n, d_hit_id, d_hit_t);
   RT_CUDA(cudaGetLastError());

@@ -160,7 +160,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   const size_t tiles_max = n1 / 2048 + 2;  // onesweep tiles are >= 2048 keys
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes ? bytes : 16); return o; };
-  size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 48), o_nodes = carve(n1 * 64);
+  size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 64), o_nodes = carve(n1 * 64);
   size_t o_refs = carve(n1 * 8), o_tp = carve((size_t)(s->nt > 0 ? s->nt : 1) * 4);
   size_t o_sun = carve((size_t)d->num_suns * sizeof(LightSun)), o_bulb = carve((size_t)d->num_bulbs * sizeof(LightBulb)),
          o_pl = carve((size_t)d->num_planes * sizeof(PlaneRec));

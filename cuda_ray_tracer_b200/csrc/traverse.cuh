@@ -24,9 +24,9 @@
 //    tmax never drops below the minimum.  So: (1) find the lexicographic minimum over ALL candidates with a
 //    near-first search that culls a subtree only when even its slack-inflated box (aux word of the node
 //    half: how far outside its AABB an accepted hit of that subtree can lie, build.cuh) is entered beyond
-//    the current hit; (2) carry the maximum exact entry distance along the path; (3) if the winner's path
-//    maximum is not strictly below its distance — a hit that lies outside one of its own boxes, ~1e-4 of
-//    rays on meshes — re-trace that ray in RT_LANE_REF.  Shadow rays to a sun need no distance test at all
+//    the current hit; (2) entry distances grow down a path, so the path condition is the leaf box's own
+//    `enter < t`; (3) if an accepted hit fails it — a hit that lies outside its own box, ~1e-4 of rays on
+//    meshes — re-trace that ray in RT_LANE_REF.  Shadow rays to a sun need no distance test at all
 //    (with tmax = +INF the reference visits every candidate until the first acceptance, so "occluded" ==
 //    "a candidate exists"); shadow rays to a bulb accept a candidate closer than the bulb only when it is
 //    consistent in the sense of (3), else they fall back as well.
@@ -60,10 +60,26 @@ __device__ __forceinline__ bool rt_slab(const float4 h0, const float4 h1, const 
   return t_enter < t_exit && (INCLUSIVE ? t_enter <= tmax : t_enter < tmax) && t_exit > 0.0001f;
 }
 
-// primitive test at sorted position k; returns true and the distance when the reference's test reports a hit
+// 256-bit read-only load (LDG.E.256 on sm_100a): one instruction per 32-byte node half / leaf record half
+#ifndef RT_USE_LD256
+#define RT_USE_LD256 1
+#endif
+__device__ __forceinline__ void rt_ld256(const float4* p, float4& a, float4& b) {
+#if !RT_USE_LD256
+  a = __ldg(p); b = __ldg(p + 1);
+  return;
+#endif
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p));
+}
+
+// primitive test at sorted position k; returns true and the distance when the reference's test reports a hit.
+// Leaf records are 64 bytes: (p0.xyz nor.x | nor.yz e1.xy) (e1.z e2.xyz | file-order index, 0, 0, 0)
 __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, const unsigned ref, const V3 o, const V3 d, float& th) {
   const unsigned k = ref & RT_LEAF_MASK;
-  const float4 a = __ldg(tv + 3 * (size_t)k);
+  float4 a, b;
+  rt_ld256(tv + RT_TV_STRIDE * (size_t)k, a, b);
   if (ref & RT_SPHERE_BIT) {  // struct.cu:64-109
     const V3 c = mk3(a.x, a.y, a.z);
     const float r2 = a.w * a.w;
@@ -78,13 +94,12 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
     th = inside ? tc + toff : tc - toff;
     return true;
   }
-  const float4 b = __ldg(tv + 3 * (size_t)k + 1);  // struct.cu:111-163
-  const V3 p0 = mk3(a.x, a.y, a.z), nor = mk3(a.w, b.x, b.y);
+  const V3 p0 = mk3(a.x, a.y, a.z), nor = mk3(a.w, b.x, b.y);  // struct.cu:111-163
   const float den = dot(d, nor);
   if (fabsf(den) < 1e-9f) return false;
   const float ti = dot(p0 - o, nor) / den;
   if (ti <= 0.001f) return false;
-  const float4 c = __ldg(tv + 3 * (size_t)k + 2);
+  const float4 c = __ldg(tv + RT_TV_STRIDE * (size_t)k + 2);
   const V3 e1 = mk3(b.z, b.w, c.x), e2 = mk3(c.y, c.z, c.w);
   const V3 pp = (ti * d + o) - p0;
   const float b1 = dot(e1, pp), b2 = dot(e2, pp);
@@ -94,115 +109,31 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
   return true;
 }
 
-// entry distance of the node half's box inflated by its hit slack plus a few ulps of the coordinates
-// involved (rounding of t*d + o and of the slab products)
-__device__ __forceinline__ float rt_enter_inflated(const float4 h0, const float4 h1, const V3 o, const V3 inv) {
-  const float s = h1.w, k = 4e-7f;
-  const float ax = fabsf(o.x) * k + s, ay = fabsf(o.y) * k + s, az = fabsf(o.z) * k + s;
-  const float x0 = h0.x - (fabsf(h0.x) * k + ax), x1 = h0.w + (fabsf(h0.w) * k + ax);
-  const float y0 = h0.y - (fabsf(h0.y) * k + ay), y1 = h1.x + (fabsf(h1.x) * k + ay);
-  const float z0 = h0.z - (fabsf(h0.z) * k + az), z1 = h1.y + (fabsf(h1.y) * k + az);
-  const float tnx = fminf((x0 - o.x) * inv.x, (x1 - o.x) * inv.x);
-  const float tny = fminf((y0 - o.y) * inv.y, (y1 - o.y) * inv.y);
-  const float tnz = fminf((z0 - o.z) * inv.z, (z1 - o.z) * inv.z);
+// Entry distance of the node half's box inflated by S = aux + omk on every side, where aux (node half word 7,
+// written by the build) = hit slack of the subtree + 4e-7 * largest |coordinate| of the box, and omk = 4e-7 *
+// largest |coordinate| of the ray origin: the slack covers accepted hits outside the box, the 4e-7 terms cover
+// the rounding of t*d + o and of the products below.  Same (b - o) * inv form as the exact test, so axis-parallel
+// rays (inv = +-INF) keep their -INF / +INF / NaN-is-ignored behaviour.
+__device__ __forceinline__ float rt_enter_inflated(const float4 h0, const float4 h1, const V3 o, const V3 inv, const float omk) {
+  const float S = h1.w + omk;
+  const float tnx = fminf((h0.x - S - o.x) * inv.x, (h0.w + S - o.x) * inv.x);
+  const float tny = fminf((h0.y - S - o.y) * inv.y, (h1.x + S - o.y) * inv.y);
+  const float tnz = fminf((h0.z - S - o.z) * inv.z, (h1.y + S - o.z) * inv.z);
   return fmaxf(fmaxf(tnx, tny), tnz);
 }
 
 struct RtStack {  // per-thread traversal stack: first RT_STACK_SHARED entries in shared memory, the rest in local memory
   unsigned (*ref)[RT_TRAV_THREADS];
-  float (*key)[RT_TRAV_THREADS];    // entry distance used for culling at pop time
-  float (*path)[RT_TRAV_THREADS];   // RT_LANE_EXACT: max exact entry distance on the path to the entry
+  float (*key)[RT_TRAV_THREADS];    // near-first lanes: entry distance used for culling at pop time
 };
 
-// hitNearest for a ray with bounce != 0 (draw.cu:292-318).  anyhit: shadow ray — only "is there a hit closer
-// than tlimit" is wanted (the reference runs a closest-hit search and looks at isHit / distance < |bulbDir|,
-// draw.cu:348-367).
-template <int MODE, bool COUNT>
-__device__ __forceinline__ RtHit rt_trace_ray(const RtDeviceScene& sc, const V3 o, const V3 d, const float tlimit, const bool anyhit,
-                                              const RtStack& S, unsigned long long& n_nodes, unsigned long long& n_leaves) {
-  constexpr bool REF = MODE == RT_LANE_REF, EXACT = MODE == RT_LANE_EXACT;
-  // reference order: tmax evolves from +INF exactly as in traverse_lbvh, tlimit only ends a shadow ray early
-  float tmax = (REF && anyhit) ? INFINITY : tlimit;
-  int best = -1;
-  float best_path = -INFINITY;
-  if (sc.n > 0) {
-    const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
-    unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
-    float loc_key[REF ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED], loc_path[EXACT ? RT_STACK_TOTAL - RT_STACK_SHARED : 1];
-    int sp = 0;
-    unsigned cur = (unsigned)sc.root;
-    float path = -INFINITY;
-    const int tid = threadIdx.x;
-    const bool want_key = !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
-    while (true) {
-      bool pop = false;
-      if (cur & RT_LEAF_BIT) {
-        if (COUNT) n_leaves++;
-        float th;
-        if (rt_prim_test(sc.sorted_tv, cur, o, d, th) && th > 1e-6f) {  // bvh_traversal.cu:80-86
-          bool take = th < tmax;
-          if (!REF && !anyhit && th == tmax && best >= 0 && (cur & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take = true;
-          if (take) {
-            if (EXACT && anyhit && tlimit != INFINITY && !(path < th)) { best = -3; break; }  // inconsistent occluder: decide in reference order
-            tmax = th; best = (int)(cur & ~RT_LEAF_BIT); best_path = path;
-            if (anyhit && th < tlimit) break;
-          }
-        }
-        pop = true;
-      } else {
-        if (COUNT) n_nodes++;
-        const float4* np = sc.nodes + 4 * (size_t)cur;
-        const float4 l0 = __ldg(np), l1 = __ldg(np + 1), r0 = __ldg(np + 2), r1 = __ldg(np + 3);
-        float el, er;
-        bool hl = rt_slab<!REF>(l0, l1, o, inv, EXACT ? INFINITY : tmax, el);
-        bool hr = rt_slab<!REF>(r0, r1, o, inv, EXACT ? INFINITY : tmax, er);
-        float kl = el, kr = er;  // culling keys
-        if (EXACT && want_key) {  // distance part of the test: exact entry first, the slack-inflated entry only when that fails
-          const float tcut = tmax * 1.000001f;  // rounding of the slab products
-          if (hl && !(el <= tmax)) { kl = rt_enter_inflated(l0, l1, o, inv); hl = kl <= tcut; }
-          if (hr && !(er <= tmax)) { kr = rt_enter_inflated(r0, r1, o, inv); hr = kr <= tcut; }
-        }
-        const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
-        if (hl && hr) {
-          unsigned far_ref = refr; float far_e = er, far_k = kr, near_e = el;
-          cur = refl;
-          if (!REF && er < el) { cur = refr; far_ref = refl; far_e = el; far_k = kl; near_e = er; }
-          if (EXACT && want_key && far_k == far_e) far_k = far_ref == refl ? rt_enter_inflated(l0, l1, o, inv) : rt_enter_inflated(r0, r1, o, inv);
-          const float far_path = fmaxf(path, far_e);
-          if (sp < RT_STACK_SHARED) { S.ref[sp][tid] = far_ref; if (!REF) S.key[sp][tid] = far_k; if (EXACT) S.path[sp][tid] = far_path; }
-          else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = far_ref; if (!REF) loc_key[sp - RT_STACK_SHARED] = far_k; if (EXACT) loc_path[sp - RT_STACK_SHARED] = far_path; }
-          if (sp < RT_STACK_TOTAL) sp++;  // bvh_traversal.cu:157-164: a push beyond 64 entries is dropped
-          else if (EXACT) { best = -3; break; }  // the reference drops a different entry: let the reference-order lane decide
-          if (EXACT) path = fmaxf(path, near_e);
-        } else if (hl) { cur = refl; if (EXACT) path = fmaxf(path, el); }
-        else if (hr) { cur = refr; if (EXACT) path = fmaxf(path, er); }
-        else pop = true;
-      }
-      if (pop) {
-        bool got = false;
-        while (sp > 0) {
-          sp--;
-          const bool in_sh = sp < RT_STACK_SHARED;
-          const float key = REF ? 0.f : (in_sh ? S.key[sp][tid] : loc_key[sp - RT_STACK_SHARED]);
-          if (REF || !(key > (EXACT ? tmax * 1.000001f : tmax))) {
-            cur = in_sh ? S.ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED];
-            if (EXACT) path = in_sh ? S.path[sp][tid] : loc_path[sp - RT_STACK_SHARED];
-            got = true; break;
-          }
-        }
-        if (!got) break;
-      }
-    }
-  }
-  if (EXACT) {
-    // certificate: the winner must be entered strictly before its own hit on every box of its path
-    if (best == -3 || (best >= 0 && !(best_path < tmax))) return rt_trace_ray<RT_LANE_REF, COUNT>(sc, o, d, tlimit, anyhit, S, n_nodes, n_leaves);
-  }
-  if (REF && anyhit && !(tmax < tlimit)) best = -1;  // closest hit is not closer than the light
+// planes live outside the BVH (checkPlane, draw.cu:581-615) and the BVH hit wins only when strictly closer
+// (hitNearest, draw.cu:304-315)
+__device__ __forceinline__ RtHit rt_finish_with_planes(const RtDeviceScene& sc, const V3 o, const V3 d, const float tlimit, const bool anyhit,
+                                                       const float tmax, const int best) {
   RtHit h;
   h.t = tmax; h.id = best;
   if (anyhit && best >= 0) return h;
-  // checkPlane, draw.cu:581-615 — planes live outside the BVH
   float t_sol = INFINITY; int pidx = -1;
   for (int p = 0; p < sc.num_planes; p++) {
     const float* pl = reinterpret_cast<const float*>(sc.planes + p);
@@ -213,44 +144,273 @@ __device__ __forceinline__ RtHit rt_trace_ray(const RtDeviceScene& sc, const V3 
   }
   const bool plane_hit = !(t_sol >= 2147483648.0f);  // t_sol >= INT_MAX - 10 (int -> float), draw.cu:609
   if (plane_hit) {
-    // draw.cu:304-315: the BVH hit wins only when strictly closer
     const bool bvh_wins = best >= 0 && tmax < t_sol;
     if (!bvh_wins && (!anyhit || t_sol < tlimit)) { h.t = t_sol; h.id = -2 - pidx; }
   }
   return h;
 }
 
+// ---- RT_LANE_REF: traverse_lbvh's own loop (bvh_traversal.cu:92-183) over the 64-byte nodes ----------------
+// anyhit: shadow ray — only "is there a hit closer than tlimit" is wanted (the reference runs a closest-hit
+// search and looks at isHit / distance < |bulbDir|, draw.cu:348-367); tmax still evolves from +INF.
+template <bool COUNT>
+__device__ __forceinline__ RtHit rt_trace_ref(const RtDeviceScene& sc, const V3 o, const V3 d, const float tlimit, const bool anyhit,
+                                           const RtStack& S, unsigned long long& n_nodes, unsigned long long& n_leaves) {
+  float tmax = INFINITY;
+  int best = -1;
+  if (sc.n > 0) {
+    const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
+    unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
+    int sp = 0;
+    unsigned cur = (unsigned)sc.root;
+    const int tid = threadIdx.x;
+    while (true) {
+      bool pop = false;
+      if (cur & RT_LEAF_BIT) {
+        if (COUNT) n_leaves++;
+        float th;
+        if (rt_prim_test(sc.sorted_tv, cur, o, d, th) && th > 1e-6f && th < tmax) {  // bvh_traversal.cu:80-86
+          tmax = th; best = (int)(cur & ~RT_LEAF_BIT);
+          if (anyhit && th < tlimit) break;
+        }
+        pop = true;
+      } else {
+        if (COUNT) n_nodes++;
+        const float4* np = sc.nodes + 4 * (size_t)cur;
+        float4 l0, l1, r0, r1;
+        rt_ld256(np, l0, l1); rt_ld256(np + 2, r0, r1);
+        float el, er;
+        const bool hl = rt_slab<false>(l0, l1, o, inv, tmax, el);
+        const bool hr = rt_slab<false>(r0, r1, o, inv, tmax, er);
+        const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
+        if (hl && hr) {  // left first, right pushed (bvh_traversal.cu:149-165)
+          cur = refl;
+          if (sp < RT_STACK_SHARED) S.ref[sp][tid] = refr;
+          else if (sp < RT_STACK_TOTAL) loc_ref[sp - RT_STACK_SHARED] = refr;
+          if (sp < RT_STACK_TOTAL) sp++;  // a push beyond 64 entries is dropped (bvh_traversal.cu:157-164)
+        } else if (hl) cur = refl;
+        else if (hr) cur = refr;
+        else pop = true;
+      }
+      if (pop) {
+        if (sp == 0) break;
+        sp--;
+        cur = sp < RT_STACK_SHARED ? S.ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED];
+      }
+    }
+  }
+  if (anyhit && !(tmax < tlimit)) best = -1;  // the closest hit is not closer than the light
+  return rt_finish_with_planes(sc, o, d, tlimit, anyhit, tmax, best);
+}
+
 // ray record: q[2r] = (origin.xyz, tlimit), q[2r+1] = (dir.xyz, bits: sample | anyhit << 31)
 #define RT_RAY_ANYHIT 0x80000000u
 
-// Persistent kernel: a fixed grid (a multiple of the SM count) of warps, each fetching 32 consecutive
-// rays at a time from the queue with one atomic per warp.
-template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned n,
-                                                                  float2* __restrict__ hits, unsigned* fetch_counter,
-                                                                  unsigned long long* stats) {
+#ifndef RT_REFILL_MIN
+#define RT_REFILL_MIN 8      // idle lanes that trigger a refill of the warp
+#endif
+#ifndef RT_LEAF_MIN
+#define RT_LEAF_MIN 8        // lanes waiting with a leaf that trigger the warp's leaf phase
+#endif
+#ifndef RT_CHUNK
+#define RT_CHUNK 256         // rays a warp reserves from the queue with one atomic
+#endif
+
+// ---- reference-order kernel: validation lane, and the exact lane's fallback list -------------------------
+// list == nullptr: all n rays of the queue, 32 at a time per warp.  list != nullptr: the rays whose indices the
+// near-first kernel appended (their hits are written here).
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned n,
+                                                                      float2* __restrict__ hits, unsigned* fetch_counter,
+                                                                      unsigned long long* stats, const unsigned* __restrict__ list,
+                                                                      const unsigned* __restrict__ list_count) {
   __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
-  __shared__ float s_key[MODE == RT_LANE_REF ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
-  __shared__ float s_path[MODE == RT_LANE_EXACT ? RT_STACK_SHARED : 1][RT_TRAV_THREADS];
-  RtStack S; S.ref = s_ref; S.key = s_key; S.path = s_path;
+  RtStack S; S.ref = s_ref; S.key = nullptr;
   const unsigned lane = threadIdx.x & 31;
+  const unsigned total = list ? *list_count : n;
   unsigned long long n_nodes = 0, n_leaves = 0;
   while (true) {
     unsigned base = 0;
     if (lane == 0) base = atomicAdd(fetch_counter, 32u);
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const unsigned r = base + lane;
-    if (r < n) {
+    if (base >= total) break;
+    const unsigned i = base + lane;
+    if (i < total) {
+      const unsigned r = list ? list[i] : i;
       const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
-      const RtHit h = rt_trace_ray<MODE, COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
-                                                (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
+      const RtHit h = rt_trace_ref<COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
+                                          (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
       __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
     }
     __syncwarp();
   }
   if (COUNT) {
-    for (int o = 16; o > 0; o >>= 1) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o); }
+    for (int o2 = 16; o2 > 0; o2 >>= 1) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o2); }
+    if (lane == 0) { atomicAdd(stats, n_nodes); atomicAdd(stats + 1, n_leaves); }
+  }
+}
+
+// ---- near-first kernel (RT_LANE_EXACT / RT_LANE_NEAR) ------------------------------------------------------
+// Persistent warps over a fixed grid (a multiple of the SM count).  Three things keep the 32 lanes busy:
+//  * rays differ a lot in length (a miss leaves after a handful of nodes, a ray through the soup takes a
+//    hundred), so a warp reserves RT_CHUNK consecutive rays with one atomic and hands them to its lanes as they
+//    finish (refill when RT_REFILL_MIN lanes are idle);
+//  * every lane is a node-by-node state machine (stack in shared memory), so a refilled lane just starts;
+//  * primitive tests are one visit in ten and as long as a node visit, so a lane that reaches leaf children
+//    parks them (after pushing the node's internal children) and the warp runs the primitive tests together
+//    once RT_LEAF_MIN lanes are parked (or nobody can continue).
+// Exact lane: rays whose winning hit fails the certificate are appended to fb_list for traverse_ref_kernel.
+template <bool EXACT, bool COUNT>
+__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned n,
+                                                                       float2* __restrict__ hits, unsigned* fetch_counter,
+                                                                       unsigned long long* stats, unsigned* __restrict__ fb_list,
+                                                                       unsigned* fb_count) {
+  __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
+  __shared__ float s_key[RT_STACK_SHARED][RT_TRAV_THREADS];
+  const unsigned lane = threadIdx.x & 31;
+  const int tid = threadIdx.x;
+  unsigned long long n_nodes = 0, n_leaves = 0;
+  unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
+  float loc_key[RT_STACK_TOTAL - RT_STACK_SHARED];
+  // lane state
+  enum { IDLE = 0, NODE = 1, LEAF = 2, DONE = 3 };
+  int st = IDLE;  // NODE: at internal node `cur`; LEAF: parked with leaf children; DONE: result ready to be written
+  bool anyhit = false, want_key = true, fallback = false;
+  unsigned r = 0, cur = 0, pend0 = 0, pend1 = 0; int sp = 0, best = -1;
+  V3 o = mk3(0, 0, 0), d = mk3(0, 0, 0), inv = mk3(0, 0, 0);
+  float tlimit = 0.f, tmax = 0.f, pe0 = 0.f, pe1 = 0.f, omk = 0.f;
+  // warp state (uniform)
+  unsigned chunk_next = 0, chunk_end = 0; bool exhausted = false;
+
+#define RT_PUSH(ref_, key_)                                                                                       \
+  do {                                                                                                            \
+    if (sp < RT_STACK_SHARED) { s_ref[sp][tid] = (ref_); s_key[sp][tid] = (key_); sp++; }                         \
+    else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
+    else fallback = true; /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
+  } while (0)
+#define RT_LEAF_TEST(ref_, e_)                                                                                    \
+  do {                                                                                                            \
+    if (COUNT) n_leaves++;                                                                                        \
+    float th_;                                                                                                    \
+    if (rt_prim_test(sc.sorted_tv, ref_, o, d, th_) && th_ > 1e-6f) { /* bvh_traversal.cu:80-86 */               \
+      bool take_ = th_ < tmax;                                                                                    \
+      if (!anyhit && th_ == tmax && best >= 0 && ((ref_) & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take_ = true; \
+      if (take_) {                                                                                                \
+        if (EXACT && want_key && !((e_) < th_)) fallback = true; /* hit outside its own box */                    \
+        tmax = th_; best = (int)((ref_) & ~RT_LEAF_BIT);                                                          \
+      }                                                                                                           \
+    }                                                                                                             \
+  } while (0)
+
+  while (true) {
+    // ---- retire finished rays and refill from the warp's chunk, RT_REFILL_MIN lanes at a time ----
+    const unsigned free_m = __ballot_sync(0xffffffffu, st == IDLE || st == DONE);
+    const unsigned busy_m = ~free_m;
+    if (free_m && (__popc(free_m) >= RT_REFILL_MIN || busy_m == 0u)) {
+      if (st == DONE) {
+        if (EXACT && fallback) fb_list[atomicAdd(fb_count, 1u)] = r;
+        else {
+          const RtHit h = rt_finish_with_planes(sc, o, d, tlimit, anyhit, tmax, best);
+          __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+        }
+        st = IDLE;
+      }
+      if (!exhausted) {
+        if (chunk_next == chunk_end) {
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(fetch_counter, (unsigned)RT_CHUNK);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (base >= n) exhausted = true;
+          else { chunk_next = base; chunk_end = min(base + (unsigned)RT_CHUNK, n); }
+        }
+        if (!exhausted) {
+          const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(free_m);
+          const unsigned take = min(avail, want), rank = (unsigned)__popc(free_m & ((1u << lane) - 1u));
+          if (st == IDLE && rank < take) {
+            r = chunk_next + rank;
+            const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
+            o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
+            anyhit = (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
+            inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
+            omk = 4e-7f * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+            tmax = tlimit; best = -1; fallback = false; sp = 0; cur = (unsigned)sc.root; pend1 = 0u;
+            want_key = !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
+            st = NODE;
+            if (sc.n <= 0) st = DONE;                                                    // planes only
+            else if (cur & RT_LEAF_BIT) { pend0 = cur; pe0 = -INFINITY; st = LEAF; }     // single primitive: the root is the leaf
+          }
+          chunk_next += take;
+        }
+      }
+    }
+    const unsigned leafm = __ballot_sync(0xffffffffu, st == LEAF), nodem = __ballot_sync(0xffffffffu, st == NODE);
+    if ((leafm | nodem) == 0u) {
+      if (__ballot_sync(0xffffffffu, st == DONE)) continue;  // retire them at the top
+      if (exhausted) break;
+      continue;
+    }
+    bool need_pop = false;
+    if (__popc(leafm) >= RT_LEAF_MIN || nodem == 0u) {
+      // ---- leaf phase ----
+      if (st == LEAF) {
+        if (pend0) RT_LEAF_TEST(pend0, pe0);
+        if (pend1 && !(anyhit && best >= 0)) RT_LEAF_TEST(pend1, pe1);
+        pend0 = pend1 = 0u;
+        if ((anyhit && best >= 0) || fallback) st = DONE; else need_pop = true;
+      }
+    } else if (st == NODE) {
+      // ---- node phase ----
+      if (COUNT) n_nodes++;
+      const float4* np = sc.nodes + 4 * (size_t)cur;
+      float4 l0, l1, r0, r1;
+      rt_ld256(np, l0, l1); rt_ld256(np + 2, r0, r1);
+      float el, er;
+      // exact lane: order-independent part of the box test here, distance part below; otherwise the full inclusive test
+      bool hl = rt_slab<true>(l0, l1, o, inv, EXACT ? INFINITY : tmax, el);
+      bool hr = rt_slab<true>(r0, r1, o, inv, EXACT ? INFINITY : tmax, er);
+      const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
+      float kl = el, kr = er;  // culling keys: what the distance test, now and at pop time, compares with tmax
+      if (EXACT && want_key) {
+        // a subtree may be skipped only if even its slack-inflated box is entered beyond the current hit
+        kl = rt_enter_inflated(l0, l1, o, inv, omk); kr = rt_enter_inflated(r0, r1, o, inv, omk);
+        const float tcut = tmax * 1.000001f;  // rounding of the products
+        hl = hl && (el <= tmax || kl <= tcut); hr = hr && (er <= tmax || kr <= tcut);
+      }
+      const bool ll = hl && (refl & RT_LEAF_BIT), lr = hr && (refr & RT_LEAF_BIT);
+      const bool il = hl && !ll, ir = hr && !lr;
+      if (ll || lr) {
+        // park the leaf children (nearer first); internal children go on the stack
+        const bool swap = ll && lr && er < el;
+        pend0 = (ll && !swap) ? refl : refr; pe0 = (ll && !swap) ? el : er;
+        pend1 = (ll && lr) ? (swap ? refl : refr) : 0u; pe1 = swap ? el : er;
+        if (il) RT_PUSH(refl, kl);
+        if (ir) RT_PUSH(refr, kr);
+        st = fallback ? DONE : LEAF;
+      } else if (il && ir) {  // nearer child next, the other on the stack
+        const bool swap = er < el;
+        cur = swap ? refr : refl;
+        RT_PUSH(swap ? refl : refr, swap ? kl : kr);
+        if (fallback) st = DONE;
+      } else if (il) cur = refl;
+      else if (ir) cur = refr;
+      else need_pop = true;
+    }
+    // ---- next node from the stack, skipping entries the current hit has made unreachable ----
+    if (need_pop) {
+      const float tcut = EXACT ? tmax * 1.000001f : tmax;
+      st = DONE;
+      while (sp > 0) {
+        sp--;
+        const bool in_sh = sp < RT_STACK_SHARED;
+        const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
+        if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; break; }
+      }
+    }
+  }
+#undef RT_PUSH
+#undef RT_LEAF_TEST
+  if (COUNT) {
+    for (int o2 = 16; o2 > 0; o2 >>= 1) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o2); }
     if (lane == 0) { atomicAdd(stats, n_nodes); atomicAdd(stats + 1, n_leaves); }
   }
 }
