@@ -126,7 +126,7 @@ def run_reference(a):
     mid = Hh // 2
     t_probe = render_rows(mid, mid + 1)
     total_steps = a.steps + a.warmup
-    rows = max(1, min(Hh // 4, int(a.cpu_seconds * 4 / max(t_probe, 1e-3) / max(total_steps, 1))))
+    rows = max(1, min(Hh // 4, int(a.cpu_seconds * 16 / max(t_probe, 1e-3) / max(total_steps, 1))))
     vals = []; secs = []
     for s in range(total_steps):
         y0 = max(0, min(Hh - rows, mid - rows // 2 + s)); y1 = y0 + rows
@@ -172,7 +172,7 @@ def cpu_baseline(a, cfg, arrays):
         return time.time() - t
 
     t_probe = go(mid, mid + 1)
-    rows = max(1, min(Hh // 8, int(a.cpu_seconds / max(t_probe, 1e-3))))
+    rows = max(1, min(Hh // 8, int(4 * a.cpu_seconds / max(t_probe, 1e-3))))
     dt = go(mid, mid + rows)
     rays = o.render(W, Hh, aa, O.SPP_REF, mid, mid + rows, cores)["counters"].rays
     return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
@@ -182,7 +182,7 @@ def cpu_baseline(a, cfg, arrays):
 def run_b200(a):
     import torch
     import torch.distributed as dist
-    from cuda_ray_tracer_b200 import api, synth
+    from cuda_ray_tracer_b200 import api, synth, parallel
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -197,9 +197,7 @@ def run_b200(a):
     p0, p1, p2 = arrays["tri"][:3]
     tp = [torch.from_numpy(x).to(dev) for x in (p0, p1, p2)]
     tm = torch.from_numpy(arrays["tri_mat"]).to(dev)
-    if world > 1:
-        for t in tp + [tm]:
-            dist.broadcast(t, 0)
+    parallel.broadcast_scene(tp + [tm], 0)
     nor, e1, e2 = api.triangle_setup(p0, p1, p2)
     arrays["tri"] = [tp[0], tp[1], tp[2]] + [torch.from_numpy(x).to(dev) for x in (nor, e1, e2)]
     arrays["tri_mat"] = tm
@@ -214,7 +212,7 @@ def run_b200(a):
     img_d = torch.zeros((Hh, W, 4), dtype=torch.uint8, device=dev)
     img_h = torch.zeros((Hh, W, 4), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    tiles = api.TileSet(32, 8, world, rank) if world > 1 else None
+    tiles = parallel.tile_set(world, rank)
     rflags = api.SPP_TRUE | api.TIME_TRAVERSE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0)
     BUILD_LAUNCHES = 1 + 8  # update_tris + init, bounds, morton, 4 onesweep passes, bottom-up
 
@@ -223,8 +221,7 @@ def run_b200(a):
         sc.update_triangles(fr[0], fr[1], fr[2])
         bms = sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
         sc.render_device(W, Hh, spp, img_d, flags=rflags, tiles=tiles, counters=cnt)
-        if world > 1:
-            dist.reduce(img_d, 0, op=dist.ReduceOp.SUM)  # tiles are disjoint and the rest is zero: sum == gather
+        parallel.gather_framebuffer(img_d, 0)  # tiles are disjoint and the rest is zero: sum == gather
         return bms
 
     def step_host(f, cnt):
@@ -233,7 +230,7 @@ def run_b200(a):
         bms = sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
         if world > 1:
             sc.render_device(W, Hh, spp, img_d, flags=rflags, tiles=tiles, counters=cnt)
-            dist.reduce(img_d, 0, op=dist.ReduceOp.SUM)
+            parallel.gather_framebuffer(img_d, 0)
             if rank == 0:
                 img_h.copy_(img_d)
         else:
