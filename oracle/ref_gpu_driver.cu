@@ -6,6 +6,13 @@
 //   --dump PREFIX       write codes / refs / nodes (reference layouts) and the RGBA image
 //   --ids               closest-hit ids of the exact-centre primary rays via material tags
 //   --w/--h/--aa        override the scene's png / aa lines;  --repeat N  re-time build and render
+//   --repair-refit      set_aabb_kernel_adapted (lbvh_builder.cu:324-387) publishes a node's box and bumps the
+//                       parent's counter with no fence in between, so on a B200 a parent can be built from a
+//                       sibling box that is not visible yet.  With this flag the driver recomputes the inner
+//                       boxes on the host from the reference's own leaf boxes and child links with the
+//                       reference's own AABB(a, b), reports how many nodes the race had left wrong
+//                       ("raced_nodes"), and uploads the result, so that the reference's traversal and shading
+//                       kernels run on the tree its build specifies.  Raw nodes go to PREFIX.nodes_raw.bin.
 // It prints one JSON object on the last stdout line.
 #include <chrono>
 #include <cstdio>
@@ -37,11 +44,31 @@ __global__ void id_kernel(int* out_kind, unsigned* out_pid, float* out_t, int W,
   out_t[tid] = o.isHit ? o.distance : INFINITY;
 }
 
+// post-order over the reference's child links; returns the number of inner nodes whose box was not the union of its children's
+static size_t repair_refit(std::vector<LBVHNode>& nodes, int N) {
+  if (N < 2) return 0;
+  std::vector<unsigned> order; order.reserve((size_t)N - 1);
+  std::vector<unsigned> st; st.push_back(0);
+  while (!st.empty()) {
+    unsigned i = st.back(); st.pop_back(); order.push_back(i);
+    unsigned l = nodes[i].left_child_offset, r = nodes[i].right_child_offset;
+    if (l < (unsigned)(N - 1)) st.push_back(l);
+    if (r < (unsigned)(N - 1)) st.push_back(r);
+  }
+  size_t bad = 0;
+  for (size_t k = order.size(); k-- > 0;) {  // children before parents
+    LBVHNode& n = nodes[order[k]];
+    AABB u(nodes[n.left_child_offset].bbox, nodes[n.right_child_offset].bbox);
+    if (memcmp(&u, &n.bbox, sizeof(AABB)) != 0) { bad++; n.bbox = u; }
+  }
+  return bad;
+}
+
 static double now() { return std::chrono::duration<double>(std::chrono::high_resolution_clock::now().time_since_epoch()).count(); }
 
 int main(int argc, char** argv) {
-  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds computed|shipped] [--dump P] [--ids] [--w W --h H --aa A] [--repeat N]\n", argv[0]); return 1; }
-  bool computed = false, ids = false; std::string dump; int W = -1, H = -1, AA = -1, repeat = 1;
+  if (argc < 2) { fprintf(stderr, "usage: %s scene.txt [--bounds computed|shipped] [--dump P] [--ids] [--w W --h H --aa A] [--repeat N] [--repair-refit]\n", argv[0]); return 1; }
+  bool computed = false, ids = false, repair = false; std::vector<size_t> raced; std::string dump; int W = -1, H = -1, AA = -1, repeat = 1;
   for (int i = 2; i < argc; i++) {
     std::string a = argv[i];
     if (a == "--bounds" && i + 1 < argc) computed = std::string(argv[++i]) == "computed";
@@ -51,6 +78,7 @@ int main(int argc, char** argv) {
     else if (a == "--h" && i + 1 < argc) H = atoi(argv[++i]);
     else if (a == "--aa" && i + 1 < argc) AA = atoi(argv[++i]);
     else if (a == "--repeat" && i + 1 < argc) repeat = atoi(argv[++i]);
+    else if (a == "--repair-refit") repair = true;
   }
   double t0 = now();
   StlConfig stl;
@@ -85,6 +113,13 @@ int main(int argc, char** argv) {
     CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
     float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
     build_ms.push_back(ms); build_wall_ms.push_back((now() - tb) * 1e3);
+    if (repair && N > 1) {
+      std::vector<LBVHNode> nodes((size_t)rc.num_lbvh_nodes);
+      CK(cudaMemcpy(nodes.data(), rc.d_lbvh_nodes, nodes.size() * sizeof(LBVHNode), cudaMemcpyDeviceToHost));
+      if (!dump.empty() && rep == repeat - 1) write_file(dump + ".nodes_raw.bin", nodes.data(), nodes.size() * sizeof(LBVHNode));
+      raced.push_back(repair_refit(nodes, N));
+      CK(cudaMemcpy(rc.d_lbvh_nodes, nodes.data(), nodes.size() * sizeof(LBVHNode), cudaMemcpyHostToDevice));
+    }
     CK(cudaMalloc(&d_rc, sizeof(RawConfig))); CK(cudaMemcpy(d_rc, &rc, sizeof(RawConfig), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&d_img, npx * sizeof(pixel_t))); CK(cudaMemset(d_img, 0, npx * sizeof(pixel_t)));
     CK(cudaDeviceSynchronize());
@@ -141,6 +176,8 @@ int main(int argc, char** argv) {
   for (size_t i = 0; i < build_wall_ms.size(); i++) printf("%s%.4f", i ? ", " : "", build_wall_ms[i]);
   printf("], \"render_s\": [");
   for (size_t i = 0; i < render_s.size(); i++) printf("%s%.6f", i ? ", " : "", render_s[i]);
+  printf("], \"raced_nodes\": [");
+  for (size_t i = 0; i < raced.size(); i++) printf("%s%zu", i ? ", " : "", raced[i]);
   printf("]}\n");
   return 0;
 }
