@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--near-first", action="store_true", help="RT_TRAVERSE_NEAR_FIRST lane (not bit-exact in rare cases)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_gpu_fast) on this GPU")
     return ap.parse_args()
 
 
@@ -179,6 +180,44 @@ def cpu_baseline(a, cfg, arrays):
             "sample": "%d image rows x %d px x %d spp (reference render() semantics) = %d rays in %.1f s" % (rows, W, aa, rays, dt)}
 
 
+def gpu_baseline(a, sc, cfg, arrays, api, synth):
+    """BASELINE.json's reported baseline: the reference's own CUDA program, compiled unmodified for sm_100
+    (oracle/_ref/ref_gpu_fast: nvcc defaults, FMA contraction on), on this GPU, same scene.  The reference renders 32
+    samples per pixel whenever aa >= 2 and has no ray counter, so both sides render the frame-0
+    scene at aa = 32 in reference sample semantics (identical images, tests/test_vs_reference_gpu.py) and the
+    ray count of this library's counters is divided by each side's time.  Rank 0, N = 1 only."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_fast")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/ref_gpu_fast was not built (needs /root/reference at build time)"}
+    import oracle_lib as O
+    p0, p1, p2 = frame_vertices(arrays, 0)
+    nor, e1, e2 = O.triangle_setup(p0, p1, p2)
+    arr = dict(arrays); arr["tri"] = [p0, p1, p2, nor, e1, e2]
+    path = "/tmp/bench_soup_%d.txt" % a.tris
+    synth.write_scene_text(path, cfg, arr, "bench_soup.png")
+    W, Hh = a.width, a.height
+    aa = 32 if a.spp >= 2 else a.spp
+    p = subprocess.run([exe, path, "--bounds", "computed", "--w", str(W), "--h", str(Hh), "--aa", str(aa), "--repeat", "3"],
+                       capture_output=True, text=True, timeout=1200, cwd="/tmp")
+    if p.returncode != 0:
+        return {"error": (p.stdout[-300:] + p.stderr[-300:])}
+    info = json.loads(p.stdout.strip().splitlines()[-1])
+    hs = api.parse_scene_file(path)          # the same text file through this library's parser
+    mine = api.Scene(hs.desc, sc.device)
+    mine.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+    best = None
+    for _ in range(3):
+        r = mine.render(W, Hh, aa, 0)
+        c = r["counters"]
+        best = c.render_ms if best is None else min(best, c.render_ms)
+    rays = c.rays
+    return {"kind": "reference CUDA build (unmodified kernels, sm_100, nvcc -O3 defaults), same B200, same scene file",
+            "workload": "soup(N=%d) frame 0, %dx%d, aa=%d in reference sample semantics (32 spp), %d rays" % (a.tris, W, Hh, aa, rays),
+            "reference_mrays_s": rays / min(info["render_s"]) / 1e6, "reference_render_s": min(info["render_s"]),
+            "reference_build_ms": min(info["build_ms"]), "reference_parse_s": info["parse_s"],
+            "b200_mrays_s": rays / best / 1e3, "b200_render_s": best * 1e-3, "host_cores": os.cpu_count()}
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -313,7 +352,7 @@ def run_b200(a):
                 "ms_per_step": e2e_res["ms"] / a.steps},
         "gpu_launches": int(dev_res["launches"]),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                     "kernel": "traverse_kernel", "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                     "kernel": "traverse_near_kernel<EXACT=%d>" % (0 if a.near_first else 1), "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "bytes_per_launch": bytes_per_launch, "ms_per_launch": ms_per_launch,
                      "share_of_step": dev_res["trav_ms"] / dev_res["ms"],
                      "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test; node and triangle arrays (64+48 MB) are mostly L2 hits, so achieved may exceed the HBM peak"},
@@ -325,6 +364,12 @@ def run_b200(a):
                                                        "refs": arrays["refs"].cpu().numpy(), "suns": arrays["suns"]})
         except Exception as e:  # the baseline is a reported figure, never the product path
             line["cpu_baseline"] = {"error": repr(e)}
+    if not a.no_gpu_baseline and world == 1:
+        try:
+            line["gpu_baseline"] = gpu_baseline(a, sc, cfg, {"tri": [p0, p1, p2], "tri_mat": arrays["tri_mat"].cpu().numpy(),
+                                                            "refs": arrays["refs"].cpu().numpy(), "suns": arrays["suns"]}, api, synth)
+        except Exception as e:
+            line["gpu_baseline"] = {"error": repr(e)}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -55,6 +55,7 @@ struct RenderBuffers {
   uint32_t* counters;     // [0] fetch ticket, [1] out-queue length, [2] overflow flag
   unsigned long long* stats;  // [0] nodes, [1] leaf tests, [2] shaded hits
   const uint32_t* rng_mats;   // power matrices P^m
+  const uint32_t* rng_nib;    // the same matrices as 4-bit lookup tables (RT_RNG_NIB_WORDS each)
   const uint32_t* rng_base;   // base vectors for mode 0/1
 };
 
@@ -113,6 +114,19 @@ __device__ __forceinline__ void queue_append(float4* __restrict__ q, uint32_t* c
   }
 }
 
+// 4-bit lookup tables of the power matrices (rng.cuh: xw_matvec_nib), built once per table upload
+__global__ void rng_nibble_kernel(const uint32_t* __restrict__ mats, int count, uint32_t* __restrict__ nib) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= count * 640) return;
+  const int m = g / 640, e = g - m * 640, p = e >> 4, v = e & 15;
+  const uint32_t* M = mats + (size_t)m * RT_RNG_MATRIX_WORDS;
+  uint32_t r[5] = {0u, 0u, 0u, 0u, 0u};
+  for (int b = 0; b < 4; b++)
+    if ((v >> b) & 1)
+      for (int k = 0; k < 5; k++) r[k] ^= M[8 * (4 * p + b) + k];
+  for (int k = 0; k < 5; k++) nib[(size_t)m * RT_RNG_NIB_WORDS + e * 5 + k] = r[k];
+}
+
 // ---- RNG seeding -------------------------------------------------------------------------------
 // mode 0/1: curand_init(1234, pixel, 0) (draw.cu:105).  Thread g handles pixel h*256 + m with m uniform
 // across the warp, so the 160 matrix rows are broadcast loads (rng.cuh).
@@ -137,8 +151,22 @@ __global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams
 }
 
 // ---- generate: RNG state, pixel jitter, primary ray (Ray::Ray(x,y,state,cfg), src/struct.cu:16-62) ---
+#define RT_GEN_CHUNKS 4   // a block generates 4 x 256 consecutive samples: the 12.8 KB skip-ahead table is staged once
 __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ uint32_t s_nib[RT_RNG_NIB_WORDS];
+  const long long base = (long long)blockIdx.x * (256 * RT_GEN_CHUNKS);
+  // sample-major order (i = sample * npix + pixel slot): a block almost always lies inside one sample index,
+  // whose skip-ahead matrix all its threads share
+  const int s0 = (int)(base / P.npix);
+  if (P.mode == 2 && s0 > 0) {
+    const uint4* src = reinterpret_cast<const uint4*>(B.rng_nib + (size_t)s0 * RT_RNG_NIB_WORDS);
+    for (int k = threadIdx.x; k < RT_RNG_NIB_WORDS / 4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
+    __syncthreads();
+  }
+  for (int chunk = 0; chunk < RT_GEN_CHUNKS; chunk++) {
+  const long long i_ll = base + chunk * 256 + threadIdx.x;
+  if (base + chunk * 256 >= P.S) break;  // block-uniform
+  const int i = (int)i_ll;
   bool live = i < P.S;
   int s = 0, lp = 0, x = 0, y = 0, pix = 0;
   if (live) {
@@ -157,8 +185,9 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     if (P.mode == 2) {  // curand_init(1234 + pixel_idx, lane_id, 0), draw.cu:162
       uint32_t v[5], d, out[5];
       xw_seed(1234ull + (unsigned long long)pix, v, d);
-      if (s) xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);
-      else { for (int k = 0; k < 5; k++) out[k] = v[k]; }
+      if (s == 0) { for (int k = 0; k < 5; k++) out[k] = v[k]; }
+      else if (s == s0) xw_matvec_nib(s_nib, v, out);
+      else xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);  // block straddling two sample indices
       rng.v0 = out[0]; rng.v1 = out[1]; rng.v2 = out[2]; rng.v3 = out[3]; rng.v4 = out[4]; rng.d = d;
       const float jx = xw_rand(-0.5f, 0.5f, rng);  // draw.cu:165-169
       const float jy = xw_rand(-0.5f, 0.5f, rng);
@@ -210,6 +239,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
   }
   queue_append(qout, B.counters + 1, has, eye, dir, INFINITY, (unsigned)i);
+  }
 }
 
 // ---- shade -------------------------------------------------------------------------------------
@@ -613,6 +643,7 @@ __global__ void unpack_hits_kernel(const float2* __restrict__ hits, const uint32
 // ---- host side -----------------------------------------------------------------------------------
 struct RngTables {  // device copies of the skip-ahead matrices, one set per device
   uint32_t* mats = nullptr; int mats_count = 0;
+  uint32_t* nib = nullptr;
   uint32_t* base = nullptr; int base_count = 0;
 };
 
@@ -693,6 +724,11 @@ int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
     if (st->rng.mats) cudaFree(st->rng.mats);
     RT_CUDA(cudaMalloc(&st->rng.mats, h.size() * 4));
     RT_CUDA(cudaMemcpy(st->rng.mats, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+    if (st->rng.nib) cudaFree(st->rng.nib);
+    RT_CUDA(cudaMalloc(&st->rng.nib, (size_t)mats_needed * RT_RNG_NIB_WORDS * 4));
+    rng_nibble_kernel<<<(mats_needed * 640 + 255) / 256, 256>>>(st->rng.mats, mats_needed, st->rng.nib);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaDeviceSynchronize());
     st->rng.mats_count = mats_needed;
   }
   if (base_needed > st->rng.base_count) {
@@ -718,7 +754,7 @@ int rt_render_free_state(rt_scene* s) {
   RenderState* st = (RenderState*)s->rstate;
   if (!st) return RT_OK;
   cudaFree(st->pool); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
-  cudaFree(st->rng.mats); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
+  cudaFree(st->rng.mats); cudaFree(st->rng.nib); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
   cudaFree(st->trace_q); cudaFree(st->trace_hits); cudaFree(st->trace_fb);
   if (st->e0) { cudaEventDestroy(st->e0); cudaEventDestroy(st->e1); cudaEventDestroy(st->t0); cudaEventDestroy(st->t1); }
   delete st;
@@ -811,7 +847,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     B.hits = (float2*)p; p += al(Smax * 8);
     B.fb_list = (unsigned*)p; p += al(Smax * 4);
   }
-  B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_base = rs->rng.base;
+  B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
   const RtDeviceScene sc = device_scene(s);
 
   RT_CUDA(cudaEventRecord(rs->e0, st));
@@ -820,7 +856,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, st));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
   RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, st));
-  uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f;
+  uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0;
   for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
     P.slot0 = (int)slot0; P.npix = (int)std::min<long long>(npix_pass, nslots - slot0); P.S = P.npix * P.spp;
     passes++;
@@ -831,7 +867,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, st>>>(P, B, hn);
       launches++;
     }
-    generate_kernel<<<(unsigned)((P.S + 255) / 256), 256, 0, st>>>(P, B, B.qa, d_hit_id);
+    generate_kernel<<<(unsigned)((P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, st>>>(P, B, B.qa, d_hit_id);
     launches++;
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 4, cudaMemcpyDeviceToHost, st));
@@ -849,8 +885,9 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
       launches += 2;
       RT_CUDA(cudaGetLastError());
-      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 8, cudaMemcpyDeviceToHost, st));
+      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 12, cudaMemcpyDeviceToHost, st));
       RT_CUDA(cudaStreamSynchronize(st));
+      fb_rays += rs->h_count[2];
       if (time_trav) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
       n_in = rs->h_count[0];
       if (rs->h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
@@ -866,6 +903,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     memset(counters, 0, sizeof(*counters));
     counters->rays = rays; counters->samples = samples; counters->wavefront_iters = iters; counters->passes = passes;
     counters->kernel_launches = launches; counters->traverse_ms = trav_ms; counters->traverse_launches = iters;
+    counters->fallback_rays = fb_rays;
     RT_CUDA(cudaEventElapsedTime(&counters->render_ms, rs->e0, rs->e1));
     unsigned long long hs[3];
     RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
@@ -931,6 +969,9 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
     unsigned long long hs[3];
     RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
     counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1];
+    unsigned fb = 0;
+    RT_CUDA(cudaMemcpy(&fb, rs->counters + 3, 4, cudaMemcpyDeviceToHost));
+    counters->fallback_rays = fb;
   }
   return RT_OK;
 }

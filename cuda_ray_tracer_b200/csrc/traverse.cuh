@@ -46,8 +46,9 @@
 struct RtHit { float t; int id; };  // id >= 0: sorted position | RT_SPHERE_BIT;  -1 miss;  -2-p plane p
 
 // hit_aabb_adapted, bvh_traversal.cu:11-44.  h0 = (xmin,ymin,zmin,xmax), h1 = (ymax,zmax,..)
+// tn = per-axis near distances (the inflated key of the exact lane is derived from them)
 template <bool INCLUSIVE>
-__device__ __forceinline__ bool rt_slab(const float4 h0, const float4 h1, const V3 o, const V3 inv, const float tmax, float& enter) {
+__device__ __forceinline__ bool rt_slab_tn(const float4 h0, const float4 h1, const V3 o, const V3 inv, const float tmax, float& enter, V3& tn) {
   const float tx1 = (h0.x - o.x) * inv.x, tx2 = (h0.w - o.x) * inv.x;
   const float tnx = fminf(tx1, tx2), tfx = fmaxf(tx1, tx2);
   const float ty1 = (h0.y - o.y) * inv.y, ty2 = (h1.x - o.y) * inv.y;
@@ -56,8 +57,13 @@ __device__ __forceinline__ bool rt_slab(const float4 h0, const float4 h1, const 
   const float tnz = fminf(tz1, tz2), tfz = fmaxf(tz1, tz2);
   const float t_enter = fmaxf(fmaxf(tnx, tny), tnz);
   const float t_exit = fminf(fminf(tfx, tfy), tfz);
-  enter = t_enter;
+  enter = t_enter; tn = mk3(tnx, tny, tnz);
   return t_enter < t_exit && (INCLUSIVE ? t_enter <= tmax : t_enter < tmax) && t_exit > 0.0001f;
+}
+template <bool INCLUSIVE>
+__device__ __forceinline__ bool rt_slab(const float4 h0, const float4 h1, const V3 o, const V3 inv, const float tmax, float& enter) {
+  V3 tn;
+  return rt_slab_tn<INCLUSIVE>(h0, h1, o, inv, tmax, enter, tn);
 }
 
 // 256-bit read-only load (LDG.E.256 on sm_100a): one instruction per 32-byte node half / leaf record half
@@ -109,17 +115,19 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
   return true;
 }
 
-// Entry distance of the node half's box inflated by S = aux + omk on every side, where aux (node half word 7,
-// written by the build) = hit slack of the subtree + 4e-7 * largest |coordinate| of the box, and omk = 4e-7 *
-// largest |coordinate| of the ray origin: the slack covers accepted hits outside the box, the 4e-7 terms cover
-// the rounding of t*d + o and of the products below.  Same (b - o) * inv form as the exact test, so axis-parallel
-// rays (inv = +-INF) keep their -INF / +INF / NaN-is-ignored behaviour.
-__device__ __forceinline__ float rt_enter_inflated(const float4 h0, const float4 h1, const V3 o, const V3 inv, const float omk) {
-  const float S = h1.w + omk;
-  const float tnx = fminf((h0.x - S - o.x) * inv.x, (h0.w + S - o.x) * inv.x);
-  const float tny = fminf((h0.y - S - o.y) * inv.y, (h1.x + S - o.y) * inv.y);
-  const float tnz = fminf((h0.z - S - o.z) * inv.z, (h1.y + S - o.z) * inv.z);
-  return fmaxf(fmaxf(tnx, tny), tnz);
+// Lower bound of the entry distance of the node half's box inflated by S = aux + omk on every side, where aux
+// (node half word 7, written by the build) = hit slack of the subtree + 4e-7 * largest |coordinate| of the box
+// and omk = 4e-7 * largest |coordinate| of the ray origin: the slack covers accepted hits outside the box, the
+// 4e-7 terms the rounding of t*d + o inside the primitive test.
+// Per axis the inflated slab is entered at tn - S/|d| in real arithmetic.  tn (the exact test's own near
+// distance, fl(fl(b - o) * inv)) carries a relative error of at most 3 ulp, inv = fl(1/d) half an ulp, so
+// key = fma(-S * 1.000001, |inv|, tn) satisfies key <= t * (1 + 3e-7) for every accepted hit t of the subtree;
+// the caller compares it with tmax * 1.000001.  Rounding is monotone, so key <= tn: the inflated test never
+// culls more than the exact one.  Axis-parallel rays (inv = +-INF): tn is -INF inside the slab (key -INF),
+// +INF outside (key NaN, dropped by fmaxf: no constraint from that axis, and the exact test fails anyway).
+__device__ __forceinline__ float rt_key_inflated(const V3 tn, const float aux, const V3 inv, const float omk) {
+  const float nS = -((aux + omk) * 1.000001f);
+  return fmaxf(fmaxf(__fmaf_rn(nS, fabsf(inv.x), tn.x), __fmaf_rn(nS, fabsf(inv.y), tn.y)), __fmaf_rn(nS, fabsf(inv.z), tn.z));
 }
 
 struct RtStack {  // per-thread traversal stack: first RT_STACK_SHARED entries in shared memory, the rest in local memory
@@ -275,10 +283,13 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
   // lane state
   enum { IDLE = 0, NODE = 1, LEAF = 2, DONE = 3 };
   int st = IDLE;  // NODE: at internal node `cur`; LEAF: parked with leaf children; DONE: result ready to be written
-  bool anyhit = false, want_key = true, fallback = false;
+  bool anyhit = false, want_key = true, fallback = false, incons = false;
   unsigned r = 0, cur = 0, pend0 = 0, pend1 = 0; int sp = 0, best = -1;
   V3 o = mk3(0, 0, 0), d = mk3(0, 0, 0), inv = mk3(0, 0, 0);
   float tlimit = 0.f, tmax = 0.f, pe0 = 0.f, pe1 = 0.f, omk = 0.f;
+  // exact lane, closest-hit rays: tcull = max(tmax, entry distance of the best hit's own leaf box) is what culling
+  // compares with, t2 = smallest accepted distance among the tested primitives other than the best (see below)
+  float tcull = 0.f, t2 = 0.f;
   // warp state (uniform)
   unsigned chunk_next = 0, chunk_end = 0; bool exhausted = false;
 
@@ -288,6 +299,15 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
     else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
     else fallback = true; /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
   } while (0)
+// Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
+// box on its path is entered before the reference's running tmax at that moment.  Entry distances grow down a
+// path, so that is implied by e_m < t* (e_m = entry of m's own leaf box; "consistent").  When e_m >= t* (the hit
+// lies outside its own box) it is still implied when every OTHER candidate c has t_c > e_m: the reference's tmax
+// is then +INF or some t_c > e_m >= enter_B on the way to m, m is accepted (t* <= e_m < t_c) and nothing later
+// beats it.  To know that, culling compares with tcull = max(t*, e_m) instead of t*, and t2 tracks the smallest
+// distance among tested candidates other than the current best (a replaced best included).  A candidate that was
+// never tested was culled with key > 1.000001 * max(t_b, e_b) of the best b of that moment: if b = m then
+// t_c > e_m; if b != m then t_c > t_b >= t2.  So t2 > e_m proves the claim; otherwise the ray goes to fb_list.
 #define RT_LEAF_TEST(ref_, e_)                                                                                    \
   do {                                                                                                            \
     if (COUNT) n_leaves++;                                                                                        \
@@ -296,19 +316,26 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
       bool take_ = th_ < tmax;                                                                                    \
       if (!anyhit && th_ == tmax && best >= 0 && ((ref_) & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take_ = true; \
       if (take_) {                                                                                                \
-        if (EXACT && want_key && !((e_) < th_)) fallback = true; /* hit outside its own box */                    \
+        if (EXACT && want_key) {                                                                                  \
+          if (anyhit) { if (!((e_) < th_)) fallback = true; } /* bulb shadow ray: first consistent occluder */    \
+          else {                                                                                                  \
+            if (best >= 0) t2 = fminf(t2, tmax);                                                                  \
+            incons = !((e_) < th_); tcull = incons ? fmaxf(th_, (e_)) : th_;                                      \
+          }                                                                                                       \
+        }                                                                                                         \
         tmax = th_; best = (int)((ref_) & ~RT_LEAF_BIT);                                                          \
-      }                                                                                                           \
+        if (!(EXACT && want_key && !anyhit)) tcull = th_;                                                         \
+      } else if (EXACT && !anyhit) t2 = fminf(t2, th_);                                                           \
     }                                                                                                             \
   } while (0)
 
   while (true) {
     // ---- retire finished rays and refill from the warp's chunk, RT_REFILL_MIN lanes at a time ----
-    const unsigned free_m = __ballot_sync(0xffffffffu, st == IDLE || st == DONE);
-    const unsigned busy_m = ~free_m;
-    if (free_m && (__popc(free_m) >= RT_REFILL_MIN || busy_m == 0u)) {
+    unsigned leafm = __ballot_sync(0xffffffffu, st == LEAF), nodem = __ballot_sync(0xffffffffu, st == NODE);
+    const unsigned free_m = ~(leafm | nodem);
+    if (free_m && (__popc(free_m) >= RT_REFILL_MIN || free_m == 0xffffffffu)) {
       if (st == DONE) {
-        if (EXACT && fallback) fb_list[atomicAdd(fb_count, 1u)] = r;
+        if (EXACT && (fallback || (incons && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;
         else {
           const RtHit h = rt_finish_with_planes(sc, o, d, tlimit, anyhit, tmax, best);
           __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
@@ -333,7 +360,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
             anyhit = (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
             omk = 4e-7f * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
-            tmax = tlimit; best = -1; fallback = false; sp = 0; cur = (unsigned)sc.root; pend1 = 0u;
+            tmax = tlimit; tcull = tlimit; t2 = INFINITY; best = -1; fallback = false; incons = false; sp = 0; cur = (unsigned)sc.root; pend1 = 0u;
             want_key = !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
             st = NODE;
             if (sc.n <= 0) st = DONE;                                                    // planes only
@@ -342,12 +369,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
           chunk_next += take;
         }
       }
-    }
-    const unsigned leafm = __ballot_sync(0xffffffffu, st == LEAF), nodem = __ballot_sync(0xffffffffu, st == NODE);
-    if ((leafm | nodem) == 0u) {
-      if (__ballot_sync(0xffffffffu, st == DONE)) continue;  // retire them at the top
-      if (exhausted) break;
-      continue;
+      leafm = __ballot_sync(0xffffffffu, st == LEAF); nodem = __ballot_sync(0xffffffffu, st == NODE);
+      if ((leafm | nodem) == 0u) {   // everybody was retired and nothing came in
+        if (exhausted) break;
+        continue;
+      }
     }
     bool need_pop = false;
     if (__popc(leafm) >= RT_LEAF_MIN || nodem == 0u) {
@@ -366,15 +392,16 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
       rt_ld256(np, l0, l1); rt_ld256(np + 2, r0, r1);
       float el, er;
       // exact lane: order-independent part of the box test here, distance part below; otherwise the full inclusive test
-      bool hl = rt_slab<true>(l0, l1, o, inv, EXACT ? INFINITY : tmax, el);
-      bool hr = rt_slab<true>(r0, r1, o, inv, EXACT ? INFINITY : tmax, er);
+      V3 tnl, tnr;
+      bool hl = rt_slab_tn<true>(l0, l1, o, inv, EXACT ? INFINITY : tmax, el, tnl);
+      bool hr = rt_slab_tn<true>(r0, r1, o, inv, EXACT ? INFINITY : tmax, er, tnr);
       const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
       float kl = el, kr = er;  // culling keys: what the distance test, now and at pop time, compares with tmax
       if (EXACT && want_key) {
         // a subtree may be skipped only if even its slack-inflated box is entered beyond the current hit
-        kl = rt_enter_inflated(l0, l1, o, inv, omk); kr = rt_enter_inflated(r0, r1, o, inv, omk);
-        const float tcut = tmax * 1.000001f;  // rounding of the products
-        hl = hl && (el <= tmax || kl <= tcut); hr = hr && (er <= tmax || kr <= tcut);
+        kl = rt_key_inflated(tnl, l1.w, inv, omk); kr = rt_key_inflated(tnr, r1.w, inv, omk);
+        const float tcut = tcull * 1.000001f;  // rounding of the products
+        hl = hl && !(kl > tcut); hr = hr && !(kr > tcut);
       }
       const bool ll = hl && (refl & RT_LEAF_BIT), lr = hr && (refr & RT_LEAF_BIT);
       const bool il = hl && !ll, ir = hr && !lr;
@@ -397,7 +424,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
     }
     // ---- next node from the stack, skipping entries the current hit has made unreachable ----
     if (need_pop) {
-      const float tcut = EXACT ? tmax * 1.000001f : tmax;
+      const float tcut = EXACT ? tcull * 1.000001f : tmax;
       st = DONE;
       while (sp > 0) {
         sp--;

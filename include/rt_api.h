@@ -119,6 +119,7 @@ typedef struct rt_counters {
   uint32_t kernel_launches; /* kernels launched by this call                                        */
   float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS / RT_TIME_TRAVERSE) */
   uint32_t traverse_launches;
+  uint64_t fallback_rays;   /* exact lane: rays re-traced in reference order (certificate failed)   */
 } rt_counters;
 int rt_render(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
               uint8_t* d_rgba, int32_t* d_hit_id, uint8_t* d_written, rt_counters* counters, void* stream);
