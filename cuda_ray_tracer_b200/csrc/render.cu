@@ -41,6 +41,7 @@ struct RenderParams {
   int slot0, npix, S;   // this pass: pixel slots [slot0, slot0+npix), S = npix * spp samples
   int depth;        // continuation stack depth (frames per sample)
   int ref_order /* traversal lane, RT_LANE_* */, rough_zyx, need_rng;
+  int rng_live;     // something after generate draws random numbers (rough materials, gi): the state is stored
   int num_lights;
 };
 
@@ -52,7 +53,8 @@ struct RenderBuffers {
   float4 *qa, *qb;        // ray queues, 2 float4 per ray
   float2* hits;           // per queue slot
   unsigned* fb_list;      // exact lane: rays to re-trace in reference order
-  uint32_t* counters;     // [0] fetch ticket, [1] out-queue length, [2] overflow flag
+  uint32_t* counters;     // [0] fetch ticket (front), [1] out-queue length (front), [2] overflow flag, [3] fallback count,
+                          // [4] fallback fetch ticket, [5] out-queue length (back), [6] fetch ticket (back)
   unsigned long long* stats;  // [0] nodes, [1] leaf tests, [2] shaded hits
   const uint32_t* rng_mats;   // power matrices P^m
   const uint32_t* rng_nib;    // the same matrices as 4-bit lookup tables (RT_RNG_NIB_WORDS each)
@@ -99,16 +101,26 @@ __device__ __forceinline__ void rng_store(const RenderBuffers& B, int i, const X
   B.rng1[i] = make_uint4(r.v4, r.d, r.bm_flag, __float_as_uint(r.bm_extra));
 }
 
-// warp-aggregated append of one ray per participating lane (called with the whole warp converged)
-__device__ __forceinline__ void queue_append(float4* __restrict__ q, uint32_t* count, bool has, V3 o, V3 d, float tlimit, unsigned tag) {
-  const unsigned m = __ballot_sync(0xffffffffu, has);
-  if (m == 0u) return;
-  const unsigned lane = threadIdx.x & 31;
-  unsigned base = 0;
-  if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(count, (unsigned)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+// warp-aggregated append of one ray per participating lane (called with the whole warp converged).
+// The queue has two ends: sun shadow rays (any hit, no distance limit) grow down from slot cap-1, everything else
+// grows up from slot 0, so that each end gets the traversal kernel specialised for it (traverse.cuh).
+__device__ __forceinline__ void queue_append(float4* __restrict__ q, uint32_t* count_front, uint32_t* count_back, unsigned cap, bool has,
+                                             V3 o, V3 d, float tlimit, unsigned tag) {
+  const bool back = has && (tag & RT_RAY_ANYHIT) && tlimit == INFINITY;
+  const unsigned mf = __ballot_sync(0xffffffffu, has && !back), mb = __ballot_sync(0xffffffffu, back);
+  if ((mf | mb) == 0u) return;
+  const unsigned lane = threadIdx.x & 31, below = (1u << lane) - 1u;
+  unsigned bf = 0, bb = 0;
+  if (mf) {
+    if (lane == (unsigned)(__ffs(mf) - 1)) bf = atomicAdd(count_front, (unsigned)__popc(mf));
+    bf = __shfl_sync(0xffffffffu, bf, __ffs(mf) - 1);
+  }
+  if (mb) {
+    if (lane == (unsigned)(__ffs(mb) - 1)) bb = atomicAdd(count_back, (unsigned)__popc(mb));
+    bb = __shfl_sync(0xffffffffu, bb, __ffs(mb) - 1);
+  }
   if (has) {
-    const size_t r = (size_t)base + __popc(m & ((1u << lane) - 1u));
+    const size_t r = back ? (size_t)cap - 1 - (bb + __popc(mb & below)) : (size_t)bf + __popc(mf & below);
     q[2 * r] = make_float4(o.x, o.y, o.z, tlimit);
     q[2 * r + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(tag));
   }
@@ -124,7 +136,13 @@ __global__ void rng_nibble_kernel(const uint32_t* __restrict__ mats, int count, 
   for (int b = 0; b < 4; b++)
     if ((v >> b) & 1)
       for (int k = 0; k < 5; k++) r[k] ^= M[8 * (4 * p + b) + k];
-  for (int k = 0; k < 5; k++) nib[(size_t)m * RT_RNG_NIB_WORDS + e * 5 + k] = r[k];
+  for (int k = 0; k < 5; k++) nib[(size_t)m * RT_RNG_NIB_STRIDE + e * 5 + k] = r[k];
+  if (e == 0) {  // M * (0, 0, v2, v3, 0) for the seed-independent words of xw_seed (seed < 2^32), rng.cuh
+    uint32_t v[5], d; xw_seed(0ull, v, d);
+    uint32_t in[5] = {0u, 0u, v[2], v[3], 0u}, c[5];
+    xw_matvec(M, in, c);
+    for (int k = 0; k < 8; k++) nib[(size_t)m * RT_RNG_NIB_STRIDE + RT_RNG_NIB_WORDS + k] = k < 5 ? c[k] : 0u;
+  }
 }
 
 // ---- RNG seeding -------------------------------------------------------------------------------
@@ -153,14 +171,14 @@ __global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams
 // ---- generate: RNG state, pixel jitter, primary ray (Ray::Ray(x,y,state,cfg), src/struct.cu:16-62) ---
 #define RT_GEN_CHUNKS 4   // a block generates 4 x 256 consecutive samples: the 12.8 KB skip-ahead table is staged once
 __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
-  __shared__ uint32_t s_nib[RT_RNG_NIB_WORDS];
+  __shared__ uint32_t s_nib[RT_RNG_NIB_STRIDE];
   const long long base = (long long)blockIdx.x * (256 * RT_GEN_CHUNKS);
   // sample-major order (i = sample * npix + pixel slot): a block almost always lies inside one sample index,
   // whose skip-ahead matrix all its threads share
   const int s0 = (int)(base / P.npix);
   if (P.mode == 2 && s0 > 0) {
-    const uint4* src = reinterpret_cast<const uint4*>(B.rng_nib + (size_t)s0 * RT_RNG_NIB_WORDS);
-    for (int k = threadIdx.x; k < RT_RNG_NIB_WORDS / 4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
+    const uint4* src = reinterpret_cast<const uint4*>(B.rng_nib + (size_t)s0 * RT_RNG_NIB_STRIDE);
+    for (int k = threadIdx.x; k < RT_RNG_NIB_STRIDE / 4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
     __syncthreads();
   }
   for (int chunk = 0; chunk < RT_GEN_CHUNKS; chunk++) {
@@ -186,7 +204,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
       uint32_t v[5], d, out[5];
       xw_seed(1234ull + (unsigned long long)pix, v, d);
       if (s == 0) { for (int k = 0; k < 5; k++) out[k] = v[k]; }
-      else if (s == s0) xw_matvec_nib(s_nib, v, out);
+      else if (s == s0) xw_matvec_nib_lowseed(s_nib, v, out);  // 1234 + pix < 2^32
       else xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);  // block straddling two sample indices
       rng.v0 = out[0]; rng.v1 = out[1]; rng.v2 = out[2]; rng.v3 = out[3]; rng.v4 = out[4]; rng.d = d;
       const float jx = xw_rand(-0.5f, 0.5f, rng);  // draw.cu:165-169
@@ -231,14 +249,14 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
       dir = fwd + sx * right + sy * up;
     }
     dir = normalize3(dir);
-    if (rng_dirty) rng_store(B, i, rng);
+    if (rng_dirty && P.rng_live) rng_store(B, i, rng);
     if (C.bounces != 0) {  // hitNearest: a ray with bounce == 0 hits nothing (draw.cu:294)
       has = true;
       B.frames[(size_t)i] = make_float4(__uint_as_float(hdr_pack(T_W_PRIMARY, C.bounces, 0u)), 1.f, 1.f, 1.f);
       B.ctl[i] = 1u;
     } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
   }
-  queue_append(qout, B.counters + 1, has, eye, dir, INFINITY, (unsigned)i);
+  queue_append(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, has, eye, dir, INFINITY, (unsigned)i);
   }
 }
 
@@ -291,11 +309,12 @@ __device__ __forceinline__ V3 rough_offset(float rough, Xorwow& rng, int zyx) {
 }
 
 __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
-                                                   const float4* __restrict__ qin, const unsigned n_in, float4* __restrict__ qout,
-                                                   int32_t* __restrict__ hit_id_out) {
-  const unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+                                                   const float4* __restrict__ qin, const unsigned n_front, const unsigned n_back,
+                                                   float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
+  const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
   bool emit = false, shaded = false; V3 eo = mk3(0, 0, 0), ed = mk3(0, 0, 0); float elimit = INFINITY; unsigned etag = 0u;
-  if (r < n_in) {
+  if (g < n_front + n_back) {
+    const unsigned r = g < n_front ? g : (unsigned)P.S - n_back + (g - n_front);  // queue slot: front end, then back end
     const float4 q0 = __ldcs(qin + 2 * (size_t)r), q1 = __ldcs(qin + 2 * (size_t)r + 1);
     const float2 hv = __ldcs(B.hits + r);
     const V3 o = mk3(q0.x, q0.y, q0.z), d = mk3(q1.x, q1.y, q1.z);
@@ -544,7 +563,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
 #undef NEED_RNG
 #undef NEED_ACC
   }
-  queue_append(qout, B.counters + 1, emit, eo, ed, elimit, etag);
+  queue_append(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, emit, eo, ed, elimit, etag);
   const unsigned sm = __ballot_sync(0xffffffffu, shaded);
   if (sm && (threadIdx.x & 31) == 0) atomicAdd(B.stats + 2, (unsigned long long)__popc(sm));
 }
@@ -671,7 +690,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
     RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
     int per_sm = 0, sms = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
     if (per_sm < 1) per_sm = 1;
     st->trav_grid = sms * per_sm;  // persistent grid: every SM full, 148 x resident CTAs on B200
@@ -698,23 +717,42 @@ RtDeviceScene device_scene(const rt_scene* s) {
 int lane_of(unsigned flags) {
   return (flags & RT_TRAVERSE_REF_ORDER) ? RT_LANE_REF : (flags & RT_TRAVERSE_NEAR_FIRST) ? RT_LANE_NEAR : RT_LANE_EXACT;
 }
-// one traversal of a ray queue: the lane's kernel, then (exact lane) the reference-order pass over the rays
-// whose certificate failed.  ctr: [0] fetch ticket, [3] fallback count, [4] fallback fetch ticket.
-void launch_traverse(int lane, bool count, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned n, float2* hits,
-                     unsigned* ctr, unsigned long long* stats, unsigned* fb_list) {
-  if (lane == RT_LANE_REF) {
-    if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, nullptr, nullptr);
-    else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, nullptr, nullptr);
-  } else if (lane == RT_LANE_NEAR) {
-    if (count) traverse_near_kernel<false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
-    else traverse_near_kernel<false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
+// one traversal of a two-ended ray queue (slots [0, nf) and [cap - nb, cap)): the lane's kernel on each end, then
+// (exact lane) the reference-order pass over the rays whose certificate failed.  Returns the number of launches.
+// ctr: [0] fetch ticket front, [3] fallback count, [4] fallback fetch ticket, [6] fetch ticket back.
+template <bool EXACT>
+void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
+                 float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count) {
+  if (sun) {
+    if (count) traverse_near_kernel<EXACT, true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
+    else traverse_near_kernel<EXACT, false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
   } else {
-    if (count) traverse_near_kernel<true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
-    else traverse_near_kernel<true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr, stats, fb_list, ctr + 3);
-    const int g2 = grid < 148 ? grid : 148;
-    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr + 4, stats, fb_list, ctr + 3);
-    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, n, hits, ctr + 4, stats, fb_list, ctr + 3);
+    if (count) traverse_near_kernel<EXACT, true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
+    else traverse_near_kernel<EXACT, false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
   }
+}
+int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned nf, unsigned nb,
+                    unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list) {
+  int launches = 0;
+  for (int end = 0; end < 2; end++) {
+    const unsigned n = end ? nb : nf, first = end ? cap - nb : 0u;
+    if (n == 0) continue;
+    unsigned* fetch = ctr + (end ? 6 : 0);
+    const int grid = (int)std::min<long long>(max_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
+    if (lane == RT_LANE_REF) {
+      if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr);
+      else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr);
+    } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3);
+    else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3);
+    launches++;
+  }
+  if (lane == RT_LANE_EXACT && nf + nb > 0) {
+    const int g2 = max_grid < 148 ? max_grid : 148;
+    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3);
+    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3);
+    launches++;
+  }
+  return launches;
 }
 
 int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
@@ -725,7 +763,7 @@ int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
     RT_CUDA(cudaMalloc(&st->rng.mats, h.size() * 4));
     RT_CUDA(cudaMemcpy(st->rng.mats, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
     if (st->rng.nib) cudaFree(st->rng.nib);
-    RT_CUDA(cudaMalloc(&st->rng.nib, (size_t)mats_needed * RT_RNG_NIB_WORDS * 4));
+    RT_CUDA(cudaMalloc(&st->rng.nib, (size_t)mats_needed * RT_RNG_NIB_STRIDE * 4));
     rng_nibble_kernel<<<(mats_needed * 640 + 255) / 256, 256>>>(st->rng.mats, mats_needed, st->rng.nib);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaDeviceSynchronize());
@@ -810,6 +848,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   const int gi = s->cfg.gi != 0 ? 1 : 0;
   P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
   if (P.depth > 200) { rt_set_error("rt_render: bounces too large for the continuation stack"); return RT_ERR_INVALID; }
+  P.rng_live = (s->any_rough || s->cfg.gi != 0) ? 1 : 0;
   P.need_rng = (P.mode != 0) || s->cfg.dof_focus != 0.0f || s->any_rough || s->cfg.gi != 0;
   if (s->cfg.fisheye || s->cfg.panorama) { if (P.mode == 0 && !s->any_rough && s->cfg.gi == 0) P.need_rng = 0; }
   P.num_lights = s->cfg.num_suns + s->cfg.num_bulbs;
@@ -856,7 +895,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, st));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
   RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, st));
-  uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0;
+  uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0; uint32_t trav_launches = 0;
   for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
     P.slot0 = (int)slot0; P.npix = (int)std::min<long long>(npix_pass, nslots - slot0); P.S = P.npix * P.spp;
     passes++;
@@ -872,24 +911,24 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));
-    unsigned n_in = rs->h_count[0];
+    unsigned n_front = rs->h_count[0], n_back = 0;  // primary rays all go to the front end
     float4 *qin = B.qa, *qout = B.qb;
-    while (n_in > 0) {
-      iters++; rays += n_in;
-      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 20, st));
+    while (n_front + n_back > 0) {
+      iters++; rays += (uint64_t)n_front + n_back;
+      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 28, st));
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t0, st));
-      const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n_in + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-      launch_traverse(P.ref_order, count, grid, st, sc, (const float4*)qin, n_in, B.hits, rs->counters, rs->stats, B.fb_list);
-      launches += P.ref_order == RT_LANE_EXACT ? 1 : 0;
+      const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, st, sc, (const float4*)qin, n_front, n_back, (unsigned)P.S, B.hits,
+                                     rs->counters, rs->stats, B.fb_list);
+      launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
-      shade_kernel<<<(n_in + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_in, qout, d_hit_id);
-      launches += 2;
+      shade_kernel<<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+      launches++;
       RT_CUDA(cudaGetLastError());
-      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 12, cudaMemcpyDeviceToHost, st));
+      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 20, cudaMemcpyDeviceToHost, st));
       RT_CUDA(cudaStreamSynchronize(st));
       fb_rays += rs->h_count[2];
       if (time_trav) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
-      n_in = rs->h_count[0];
+      n_front = rs->h_count[0]; n_back = rs->h_count[4];
       if (rs->h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
       std::swap(qin, qout);
     }
@@ -902,7 +941,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (counters) {
     memset(counters, 0, sizeof(*counters));
     counters->rays = rays; counters->samples = samples; counters->wavefront_iters = iters; counters->passes = passes;
-    counters->kernel_launches = launches; counters->traverse_ms = trav_ms; counters->traverse_launches = iters;
+    counters->kernel_launches = launches; counters->traverse_ms = trav_ms; counters->traverse_launches = trav_launches;
     counters->fallback_rays = fb_rays;
     RT_CUDA(cudaEventElapsedTime(&counters->render_ms, rs->e0, rs->e1));
     unsigned long long hs[3];
@@ -951,12 +990,12 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   }
   const bool count = (flags & RT_COUNTERS) != 0;
   const RtDeviceScene sc = device_scene(s);
-  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 20, st));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 28, st));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
   pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
   RT_CUDA(cudaEventRecord(rs->e0, st));
-  const int grid = (int)std::min<long long>(rs->trav_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
-  launch_traverse(lane_of(flags), count, grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, rs->trace_hits, rs->counters, rs->stats, rs->trace_fb);
+  launch_traverse(lane_of(flags), count, rs->trav_grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, 0u, (unsigned)n, rs->trace_hits, rs->counters,
+                  rs->stats, rs->trace_fb);
   RT_CUDA(cudaEventRecord(rs->e1, st));
   unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(rs->trace_hits, s->sorted_perm, n, d_hit_id, d_hit_t);
   RT_CUDA(cudaGetLastError());

@@ -7,6 +7,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#define RT_RNG_NIB_WORDS (40 * 16 * 5)   // 4-bit lookup table of one skip-ahead matrix (xw_matvec_nib), words
+#define RT_RNG_NIB_STRIDE (RT_RNG_NIB_WORDS + 8)  // + the constant vector of xw_matvec_nib_lowseed, padded to 32 bytes
+
 struct Xorwow {
   uint32_t v0, v1, v2, v3, v4, d;
   uint32_t bm_flag;   // EXTRA_FLAG_NORMAL = 1 when a cached Box-Muller value is pending
@@ -70,12 +73,29 @@ __device__ __forceinline__ void xw_matvec(const uint32_t* __restrict__ M, const 
   }
   out[0] = r0; out[1] = r1; out[2] = r2; out[3] = r3; out[4] = r4;
 }
+// Seeds below 2^32 (1234 + pixel always is) leave state words v2, v3 of xw_seed independent of the seed, so their
+// share of the product is one constant vector per matrix (tab[RT_RNG_NIB_WORDS .. +5), written by the table
+// kernel) and only the 24 nibbles of v0, v1, v4 are looked up.
+__device__ __forceinline__ void xw_matvec_nib_lowseed(const uint32_t* tab, const uint32_t* in, uint32_t* out) {
+  uint32_t r0 = tab[RT_RNG_NIB_WORDS], r1 = tab[RT_RNG_NIB_WORDS + 1], r2 = tab[RT_RNG_NIB_WORDS + 2], r3 = tab[RT_RNG_NIB_WORDS + 3],
+           r4 = tab[RT_RNG_NIB_WORDS + 4];
+#pragma unroll
+  for (int ii = 0; ii < 3; ii++) {
+    const int i = ii == 2 ? 4 : ii;
+    const uint32_t w = in[i];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const uint32_t* e = tab + ((i * 8 + j) * 16 + ((w >> (4 * j)) & 15u)) * 5;
+      r0 ^= e[0]; r1 ^= e[1]; r2 ^= e[2]; r3 ^= e[3]; r4 ^= e[4];
+    }
+  }
+  out[0] = r0; out[1] = r1; out[2] = r2; out[3] = r3; out[4] = r4;
+}
 
 // The same product through 4-bit tables (method of the four Russians): T[p][v] = XOR of the rows 4p+b, b in v,
 // 40 nibble positions x 16 values x 5 words = 12.8 KB per matrix, staged in shared memory by the caller.  An
 // entry is 5 words, so the 16 entries of a position start in 16 different banks: lanes with different nibble
 // values do not conflict, lanes with equal values broadcast.  40 x (5 loads + 5 xors) instead of 160 x.
-#define RT_RNG_NIB_WORDS (40 * 16 * 5)
 __device__ __forceinline__ void xw_matvec_nib(const uint32_t* tab, const uint32_t* in, uint32_t* out) {
   uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
 #pragma unroll

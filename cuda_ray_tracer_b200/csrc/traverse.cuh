@@ -36,8 +36,12 @@
 #include "common.cuh"
 #include "rt_math.cuh"
 
+#ifndef RT_TRAV_THREADS
 #define RT_TRAV_THREADS 128
+#endif
+#ifndef RT_STACK_SHARED
 #define RT_STACK_SHARED 12   // entries per thread kept in shared memory
+#endif
 #define RT_LANE_REF 0
 #define RT_LANE_NEAR 1
 #define RT_LANE_EXACT 2
@@ -100,19 +104,19 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
     th = inside ? tc + toff : tc - toff;
     return true;
   }
-  const V3 p0 = mk3(a.x, a.y, a.z), nor = mk3(a.w, b.x, b.y);  // struct.cu:111-163
-  const float den = dot(d, nor);
-  if (fabsf(den) < 1e-9f) return false;
-  const float ti = dot(p0 - o, nor) / den;
-  if (ti <= 0.001f) return false;
+  // struct.cu:111-163.  The reference returns at the first failed condition; here every quantity is computed and
+  // the conditions are combined at the end, so the lanes of a leaf phase stay together (a lane that fails early
+  // would only idle).  den == 0 gives ti = +-INF or NaN, which the |den| condition masks.
   const float4 c = __ldg(tv + RT_TV_STRIDE * (size_t)k + 2);
+  const V3 p0 = mk3(a.x, a.y, a.z), nor = mk3(a.w, b.x, b.y);
+  const float den = dot(d, nor);
+  const float ti = dot(p0 - o, nor) / den;
   const V3 e1 = mk3(b.z, b.w, c.x), e2 = mk3(c.y, c.z, c.w);
   const V3 pp = (ti * d + o) - p0;
   const float b1 = dot(e1, pp), b2 = dot(e2, pp);
   const float b0 = 1.0f - b1 - b2;
-  if (!((b0 >= -0.001f) && (b1 >= -0.001f) && (b2 >= -0.001f))) return false;
   th = ti;
-  return true;
+  return !(fabsf(den) < 1e-9f) && !(ti <= 0.001f) && (b0 >= -0.001f) && (b1 >= -0.001f) && (b2 >= -0.001f);
 }
 
 // Lower bound of the entry distance of the node half's box inflated by S = aux + omk on every side, where aux
@@ -221,15 +225,15 @@ __device__ __forceinline__ RtHit rt_trace_ref(const RtDeviceScene& sc, const V3 
 #define RT_LEAF_MIN 8        // lanes waiting with a leaf that trigger the warp's leaf phase
 #endif
 #ifndef RT_CHUNK
-#define RT_CHUNK 256         // rays a warp reserves from the queue with one atomic
+#define RT_CHUNK 64          // rays a warp reserves from the queue with one atomic (swept 32..1024 on the 1M soup)
 #endif
 
 // ---- reference-order kernel: validation lane, and the exact lane's fallback list -------------------------
-// list == nullptr: all n rays of the queue, 32 at a time per warp.  list != nullptr: the rays whose indices the
+// list == nullptr: the n rays of the queue from slot `first`, 32 at a time per warp.  list != nullptr: the rays whose indices the
 // near-first kernel appended (their hits are written here).
 template <bool COUNT>
-__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned n,
-                                                                      float2* __restrict__ hits, unsigned* fetch_counter,
+__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
+                                                                      const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                       unsigned long long* stats, const unsigned* __restrict__ list,
                                                                       const unsigned* __restrict__ list_count) {
   __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
@@ -244,7 +248,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
     if (base >= total) break;
     const unsigned i = base + lane;
     if (i < total) {
-      const unsigned r = list ? list[i] : i;
+      const unsigned r = list ? list[i] : first + i;
       const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
       const RtHit h = rt_trace_ref<COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
                                           (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
@@ -268,9 +272,12 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 //    parks them (after pushing the node's internal children) and the warp runs the primitive tests together
 //    once RT_LEAF_MIN lanes are parked (or nobody can continue).
 // Exact lane: rays whose winning hit fails the certificate are appended to fb_list for traverse_ref_kernel.
-template <bool EXACT, bool COUNT>
-__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned n,
-                                                                       float2* __restrict__ hits, unsigned* fetch_counter,
+// SUN: the queue end that holds only sun shadow rays (any hit, no distance limit).  Their answer is "does a
+// candidate exist", whatever the order, so this instantiation carries no culling keys at all: the exact box test
+// decides, the stack holds references only, a pop is a pop.
+template <bool EXACT, bool COUNT, bool SUN>
+__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
+                                                                       const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
                                                                        unsigned* fb_count) {
   __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
@@ -295,8 +302,8 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
 
 #define RT_PUSH(ref_, key_)                                                                                       \
   do {                                                                                                            \
-    if (sp < RT_STACK_SHARED) { s_ref[sp][tid] = (ref_); s_key[sp][tid] = (key_); sp++; }                         \
-    else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
+    if (sp < RT_STACK_SHARED) { s_ref[sp][tid] = (ref_); if (!SUN) s_key[sp][tid] = (key_); sp++; }               \
+    else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); if (!SUN) loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
     else fallback = true; /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
   } while (0)
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
@@ -348,7 +355,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
           if (lane == 0) base = atomicAdd(fetch_counter, (unsigned)RT_CHUNK);
           base = __shfl_sync(0xffffffffu, base, 0);
           if (base >= n) exhausted = true;
-          else { chunk_next = base; chunk_end = min(base + (unsigned)RT_CHUNK, n); }
+          else { chunk_next = first + base; chunk_end = first + min(base + (unsigned)RT_CHUNK, n); }
         }
         if (!exhausted) {
           const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(free_m);
@@ -357,11 +364,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
             r = chunk_next + rank;
             const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
             o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
-            anyhit = (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
+            anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
             omk = 4e-7f * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
             tmax = tlimit; tcull = tlimit; t2 = INFINITY; best = -1; fallback = false; incons = false; sp = 0; cur = (unsigned)sc.root; pend1 = 0u;
-            want_key = !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
+            want_key = !SUN && !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
             st = NODE;
             if (sc.n <= 0) st = DONE;                                                    // planes only
             else if (cur & RT_LEAF_BIT) { pend0 = cur; pe0 = -INFINITY; st = LEAF; }     // single primitive: the root is the leaf
@@ -393,44 +400,49 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
       float el, er;
       // exact lane: order-independent part of the box test here, distance part below; otherwise the full inclusive test
       V3 tnl, tnr;
-      bool hl = rt_slab_tn<true>(l0, l1, o, inv, EXACT ? INFINITY : tmax, el, tnl);
-      bool hr = rt_slab_tn<true>(r0, r1, o, inv, EXACT ? INFINITY : tmax, er, tnr);
+      bool hl = rt_slab_tn<true>(l0, l1, o, inv, (EXACT || SUN) ? INFINITY : tmax, el, tnl);
+      bool hr = rt_slab_tn<true>(r0, r1, o, inv, (EXACT || SUN) ? INFINITY : tmax, er, tnr);
       const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
       float kl = el, kr = er;  // culling keys: what the distance test, now and at pop time, compares with tmax
-      if (EXACT && want_key) {
+      if (EXACT && !SUN) {
         // a subtree may be skipped only if even its slack-inflated box is entered beyond the current hit
+        // (sun shadow rays: tcull stays +INF, nothing is culled by distance)
         kl = rt_key_inflated(tnl, l1.w, inv, omk); kr = rt_key_inflated(tnr, r1.w, inv, omk);
         const float tcut = tcull * 1.000001f;  // rounding of the products
         hl = hl && !(kl > tcut); hr = hr && !(kr > tcut);
       }
-      const bool ll = hl && (refl & RT_LEAF_BIT), lr = hr && (refr & RT_LEAF_BIT);
-      const bool il = hl && !ll, ir = hr && !lr;
-      if (ll || lr) {
-        // park the leaf children (nearer first); internal children go on the stack
-        const bool swap = ll && lr && er < el;
-        pend0 = (ll && !swap) ? refl : refr; pe0 = (ll && !swap) ? el : er;
-        pend1 = (ll && lr) ? (swap ? refl : refr) : 0u; pe1 = swap ? el : er;
-        if (il) RT_PUSH(refl, kl);
-        if (ir) RT_PUSH(refr, kr);
-        st = fallback ? DONE : LEAF;
-      } else if (il && ir) {  // nearer child next, the other on the stack
-        const bool swap = er < el;
-        cur = swap ? refr : refl;
-        RT_PUSH(swap ? refl : refr, swap ? kl : kr);
-        if (fallback) st = DONE;
-      } else if (il) cur = refl;
-      else if (ir) cur = refr;
-      else need_pop = true;
+      // One straight-line decision (selects, one push site) instead of a branch per case:
+      //  * leaf children are parked, nearer first; the internal child beside them (at most one) goes on the stack;
+      //  * two internal children: continue with the nearer, push the other;  one: continue with it;  none: pop.
+      const bool leafl = (refl & RT_LEAF_BIT) != 0u, leafr = (refr & RT_LEAF_BIT) != 0u;
+      const bool ll = hl && leafl, lr = hr && leafr, il = hl && !leafl, ir = hr && !leafr;
+      const bool near_r = er < el;
+      const bool both_i = il && ir, any_l = ll || lr, any_i = il || ir;
+      const bool sw_l = ll && lr && near_r, first_l = ll && !sw_l;
+      pend0 = any_l ? (first_l ? refl : refr) : 0u; pe0 = first_l ? el : er;
+      pend1 = (ll && lr) ? (sw_l ? refl : refr) : 0u; pe1 = sw_l ? el : er;
+      const bool take_r = both_i ? near_r : ir;
+      const bool push_do = any_l ? any_i : both_i;
+      const bool push_r = any_l ? ir : !near_r;
+      if (push_do) RT_PUSH(push_r ? refr : refl, push_r ? kr : kl);
+      cur = take_r ? refr : refl;
+      st = any_l ? LEAF : NODE;
+      need_pop = !any_l && !any_i;
+      if (fallback) { st = DONE; need_pop = false; }  // stack overflow: the reference-order pass decides
     }
     // ---- next node from the stack, skipping entries the current hit has made unreachable ----
     if (need_pop) {
-      const float tcut = EXACT ? tcull * 1.000001f : tmax;
       st = DONE;
-      while (sp > 0) {
-        sp--;
-        const bool in_sh = sp < RT_STACK_SHARED;
-        const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
-        if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; break; }
+      if (SUN) {
+        if (sp > 0) { sp--; cur = sp < RT_STACK_SHARED ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; }
+      } else {
+        const float tcut = EXACT ? tcull * 1.000001f : tmax;
+        while (sp > 0) {
+          sp--;
+          const bool in_sh = sp < RT_STACK_SHARED;
+          const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
+          if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; break; }
+        }
       }
     }
   }
