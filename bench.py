@@ -61,29 +61,47 @@ def frame_vertices(arrays, frame):
 
 
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons sampled DURING the timed region: NVML every 20 ms (nvidia-smi, the recipe's
+    command, as the fallback: it needs ~100 ms per query, too slow for a sub-second timed region)."""
+    REASONS = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index = index; self.rows = []; self.stop_flag = False
+        self.index = index; self.sm = []; self.mx = []; self.mask = 0; self.stop_flag = False; self.how = "nvml"
 
     def run(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)))
+            while not self.stop_flag:
+                self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                try:
+                    self.mask |= int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    self.mask |= int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                time.sleep(0.02)
+            return
+        except Exception:
+            self.how = "nvidia-smi"
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                r = [x.strip() for x in out.split(",")]
+                self.sm.append(float(r[0])); self.mx.append(float(r[1]))
+                for k, (_, bit) in enumerate(self.REASONS):
+                    if r[2 + k].lower().startswith("active"):
+                        self.mask |= bit
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": [n for n, bit in self.REASONS if self.mask & bit], "samples": len(self.sm), "how": self.how}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -173,8 +191,11 @@ def cpu_baseline(a, cfg, arrays):
         return time.time() - t
 
     t_probe = go(mid, mid + 1)
-    rows = max(1, min(Hh // 8, int(4 * a.cpu_seconds / max(t_probe, 1e-3))))
+    rows = max(1, min(Hh // 8, int(a.cpu_seconds / max(t_probe, 1e-3))))
     dt = go(mid, mid + rows)
+    if dt < 0.6 * a.cpu_seconds and rows < Hh // 8:  # the 1-row probe overestimates (thread start-up): rescale once
+        rows = max(rows, min(Hh // 8, int(rows * a.cpu_seconds / max(dt, 1e-3))))
+        dt = go(mid, mid + rows)
     rays = o.render(W, Hh, aa, O.SPP_REF, mid, mid + rows, cores)["counters"].rays
     return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
             "sample": "%d image rows x %d px x %d spp (reference render() semantics) = %d rays in %.1f s" % (rows, W, aa, rays, dt)}
