@@ -352,6 +352,11 @@ def run_b200(a):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this command
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traverse_r01.json")))["dram_bytes_per_launch_mean"]
+    except Exception:
+        pass
     # per-launch figures: algorithmic bytes of one frame / traverse launches of one frame; duration = live CUDA-event average
     launches_per_frame = dev_res["trav_launches"] / a.steps
     bytes_per_launch = alg[0].item() / world / max(launches_per_frame, 1)   # per rank, like the per-rank event time
@@ -372,7 +377,8 @@ def run_b200(a):
         "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 3 * 12 * n * world, "d2h_bytes_per_step": W * Hh * 4,
                 "ms_per_step": e2e_res["ms"] / a.steps},
         "gpu_launches": int(dev_res["launches"]),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_note": "dram__bytes_read+write per launch, mean of the 4 launches in profiles/ncu_traverse_r01.json: the ray records in and the hits out; node and leaf fetches hit in L2",
                      "kernel": "traverse_near_kernel<EXACT=%d>" % (0 if a.near_first else 1), "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "bytes_per_launch": bytes_per_launch, "ms_per_launch": ms_per_launch,
                      "share_of_step": dev_res["trav_ms"] / dev_res["ms"],
