@@ -71,9 +71,13 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
   // gather the trace view into Morton order (leaf k <-> record k)
   const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
-  { float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k; rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f); }
   RtBox box = rt_prim_box(a, b, c);
-  float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
+  {
+    float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
+    rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.zmin, box.xmax); rec[5] = make_float4(box.ymax, box.zmax, 0.f, 0.f);
+  }
+  float slack = c.y;  // hit slack of the primitive, computed with the triangle setup (scene.cu, build.cuh)
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
   Delta<KeyT> D{keys, n};
   int l = k, r = k;
@@ -155,9 +159,13 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   const uint32_t p = perm[k];
   const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
   const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
-  { float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k; rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f); }
   RtBox box = rt_prim_box(a, b, c);
-  float slack = rt_leaf_slack(a, b, c, t0, t1, t2, box);
+  {
+    float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
+    rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.zmin, box.xmax); rec[5] = make_float4(box.ymax, box.zmax, 0.f, 0.f);
+  }
+  float slack = c.y;  // hit slack of the primitive, computed with the triangle setup (scene.cu, build.cuh)
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
   if (n == 1) { *root_out = (int)ref; root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax; return; }
   int pi = parent[n - 1 + k];

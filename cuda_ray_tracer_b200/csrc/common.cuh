@@ -1,13 +1,15 @@
 // common.cuh — internal types of libb200rt.so (device data layout, error handling).
 //
 // Data layout in HBM (all arrays 256-byte aligned inside one arena):
-//   prim_bv  [n][3] float4  "build view", file order.   triangle: p0.xyz p1.x | p1.yz p2.xy | p2.z 0 0 tag
-//                                                      sphere:   c.xyz r      | 0 0 0 0     | 0 0 0 tag
+//   prim_bv  [n][3] float4  "build view", file order.   triangle: p0.xyz p1.x | p1.yz p2.xy | p2.z slack 0 tag
+//                                                      sphere:   c.xyz r      | 0 0 0 0     | 0 slack 0 tag
 //   prim_tv  [n][3] float4  "trace view", file order.   triangle: p0.xyz nor.x | nor.yz e1.xy | e1.z e2.xyz
 //                                                      sphere:   c.xyz r      | 0 ...
 //   prim_mat [n][3] float4  Materials (11 floats + pad), file order
-//   sorted_tv[n][4] float4  prim_tv gathered into Morton order (leaf k reads record k), 64-byte records:
-//                            the three prim_tv words + (file-order index, 0, 0, 0)
+//   sorted_tv[n][6] float4  prim_tv gathered into Morton order (leaf k reads record k), 96-byte records:
+//                            the three prim_tv words + (file-order index, 0, 0, 0) | the leaf's own AABB in node-half
+//                            layout (xmin ymin zmin xmax | ymax zmax 0 0): read only when a hit is accepted, for the
+//                            exact lane's certificate (traverse.cuh)
 //   nodes    [n-1][4] float4 64-byte internal node = two 32-byte child halves
 //                            half: min.xyz max.x | max.yz ref aux      (ref<0: leaf, see below)
 // Everything the tracer touches is indexed by file-order primitive index or by sorted position;
@@ -20,7 +22,7 @@
 
 #include "../../include/rt_api.h"
 
-#define RT_TV_STRIDE 4  // float4 words per sorted leaf record
+#define RT_TV_STRIDE 6  // float4 words per sorted leaf record (96 bytes = three 32-byte sectors)
 #define RT_TAG_TRI 1.0f
 #define RT_TAG_SPHERE 2.0f
 

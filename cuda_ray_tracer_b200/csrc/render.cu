@@ -693,6 +693,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
     RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
     if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("RT_TRAV_CTAS_PER_SM")) { const int v = atoi(e); if (v >= 1 && v < per_sm) per_sm = v; }  // experiments
     st->trav_grid = sms * per_sm;  // persistent grid: every SM full, 148 x resident CTAs on B200
   }
   return RT_OK;

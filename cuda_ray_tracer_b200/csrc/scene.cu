@@ -6,7 +6,7 @@
 #include <mutex>
 #include <vector>
 
-#include "common.cuh"
+#include "build.cuh"
 
 static thread_local std::string g_err;
 void rt_set_error(const std::string& msg) { g_err = msg; }
@@ -32,7 +32,7 @@ __global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* ma
     float rad = a.sr[r.y];
     bv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
     bv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-    bv[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, RT_TAG_SPHERE);
+    bv[3 * (size_t)i + 2] = make_float4(0.f, 2e-3f * fabsf(rad), 0.f, RT_TAG_SPHERE);  // .y = hit slack (build.cuh)
     tv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
     tv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     tv[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -43,10 +43,13 @@ __global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* ma
                 *e2 = a.te2 + 3 * t;
     bv[3 * (size_t)i + 0] = make_float4(p0[0], p0[1], p0[2], p1[0]);
     bv[3 * (size_t)i + 1] = make_float4(p1[1], p1[2], p2[0], p2[1]);
-    bv[3 * (size_t)i + 2] = make_float4(p2[2], 0.f, 0.f, RT_TAG_TRI);
-    tv[3 * (size_t)i + 0] = make_float4(p0[0], p0[1], p0[2], nn[0]);
-    tv[3 * (size_t)i + 1] = make_float4(nn[1], nn[2], e1[0], e1[1]);
-    tv[3 * (size_t)i + 2] = make_float4(e1[2], e2[0], e2[1], e2[2]);
+    const float4 ba = make_float4(p0[0], p0[1], p0[2], p1[0]), bb = make_float4(p1[1], p1[2], p2[0], p2[1]);
+    float4 bc = make_float4(p2[2], 0.f, 0.f, RT_TAG_TRI);
+    const float4 ta = make_float4(p0[0], p0[1], p0[2], nn[0]), tb = make_float4(nn[1], nn[2], e1[0], e1[1]),
+                 tc = make_float4(e1[2], e2[0], e2[1], e2[2]);
+    bc.y = rt_leaf_slack(ba, bb, bc, ta, tb, tc, rt_prim_box(ba, bb, bc));  // hit slack, a property of the triangle setup
+    bv[3 * (size_t)i + 2] = bc;
+    tv[3 * (size_t)i + 0] = ta; tv[3 * (size_t)i + 1] = tb; tv[3 * (size_t)i + 2] = tc;
     tri_prim[t] = (uint32_t)i;
     m = a.tm + 11 * t;
   }
@@ -106,12 +109,12 @@ __global__ void update_tris_kernel(int nt, const float* p0a, const float* p1a, c
   float s1 = 1.0f / dot3(a1, sub3(p1, p0)), s2 = 1.0f / dot3(a2, sub3(p2, p0));
   float3 e1 = f3(a1.x * s1, a1.y * s1, a1.z * s1), e2 = f3(a2.x * s2, a2.y * s2, a2.z * s2);
   size_t i = tri_prim[t];
-  bv[3 * i + 0] = make_float4(p0.x, p0.y, p0.z, p1.x);
-  bv[3 * i + 1] = make_float4(p1.y, p1.z, p2.x, p2.y);
-  bv[3 * i + 2] = make_float4(p2.z, 0.f, 0.f, RT_TAG_TRI);
-  tv[3 * i + 0] = make_float4(p0.x, p0.y, p0.z, nor.x);
-  tv[3 * i + 1] = make_float4(nor.y, nor.z, e1.x, e1.y);
-  tv[3 * i + 2] = make_float4(e1.z, e2.x, e2.y, e2.z);
+  const float4 ba = make_float4(p0.x, p0.y, p0.z, p1.x), bb = make_float4(p1.y, p1.z, p2.x, p2.y);
+  float4 bc = make_float4(p2.z, 0.f, 0.f, RT_TAG_TRI);
+  const float4 ta = make_float4(p0.x, p0.y, p0.z, nor.x), tb = make_float4(nor.y, nor.z, e1.x, e1.y), tc = make_float4(e1.z, e2.x, e2.y, e2.z);
+  bc.y = rt_leaf_slack(ba, bb, bc, ta, tb, tc, rt_prim_box(ba, bb, bc));  // hit slack travels with the triangle setup
+  bv[3 * i + 0] = ba; bv[3 * i + 1] = bb; bv[3 * i + 2] = bc;
+  tv[3 * i + 0] = ta; tv[3 * i + 1] = tb; tv[3 * i + 2] = tc;
 }
 
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -160,7 +163,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   const size_t tiles_max = n1 / 2048 + 2;  // onesweep tiles are >= 2048 keys
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes ? bytes : 16); return o; };
-  size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 64), o_nodes = carve(n1 * 64);
+  size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 16 * RT_TV_STRIDE), o_nodes = carve(n1 * 64);
   size_t o_refs = carve(n1 * 8), o_tp = carve((size_t)(s->nt > 0 ? s->nt : 1) * 4);
   size_t o_sun = carve((size_t)d->num_suns * sizeof(LightSun)), o_bulb = carve((size_t)d->num_bulbs * sizeof(LightBulb)),
          o_pl = carve((size_t)d->num_planes * sizeof(PlaneRec));

@@ -263,37 +263,45 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 }
 
 // ---- near-first kernel (RT_LANE_EXACT / RT_LANE_NEAR) ------------------------------------------------------
-// Persistent warps over a fixed grid (a multiple of the SM count).  Three things keep the 32 lanes busy:
+// Persistent warps over a fixed grid (a multiple of the SM count).  The kernel is instruction-issue bound (ncu:
+// 75 % of issue slots, ALU pipe 65 %, DRAM 1 %), so the structure is chosen for few instructions per step and
+// many lanes per instruction:
 //  * rays differ a lot in length (a miss leaves after a handful of nodes, a ray through the soup takes a
 //    hundred), so a warp reserves RT_CHUNK consecutive rays with one atomic and hands them to its lanes as they
 //    finish (refill when RT_REFILL_MIN lanes are idle);
-//  * every lane is a node-by-node state machine (stack in shared memory), so a refilled lane just starts;
-//  * primitive tests are one visit in ten and as long as a node visit, so a lane that reaches leaf children
-//    parks them (after pushing the node's internal children) and the warp runs the primitive tests together
-//    once RT_LEAF_MIN lanes are parked (or nobody can continue).
+//  * every lane is a step-by-step state machine (stack in shared memory) whose whole position is `cur`: an
+//    internal node slot, or a leaf reference (bit 31).  Leaf children are not special in a node step: the nearer
+//    hit child becomes `cur`, the other is pushed with its culling key;
+//  * a primitive test is as long as a node step and happens once in ten steps, so lanes that arrive at a leaf
+//    wait and the warp runs the tests together once RT_LEAF_MIN lanes are there (or nobody can continue);
+//  * the certificate needs the entry distance of the winning leaf's own box: the 96-byte leaf record carries the
+//    box in its third sector, read only when a hit is accepted (about once per ray).
 // Exact lane: rays whose winning hit fails the certificate are appended to fb_list for traverse_ref_kernel.
 // SUN: the queue end that holds only sun shadow rays (any hit, no distance limit).  Their answer is "does a
 // candidate exist", whatever the order, so this instantiation carries no culling keys at all: the exact box test
 // decides, the stack holds references only, a pop is a pop.
+#ifndef RT_TRAV_MIN_CTAS
+#define RT_TRAV_MIN_CTAS 1
+#endif
 template <bool EXACT, bool COUNT, bool SUN>
-__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
+__global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
                                                                        const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
                                                                        unsigned* fb_count) {
   __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
-  __shared__ float s_key[RT_STACK_SHARED][RT_TRAV_THREADS];
+  __shared__ float s_key[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
   const unsigned lane = threadIdx.x & 31;
   const int tid = threadIdx.x;
   unsigned long long n_nodes = 0, n_leaves = 0;
   unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
-  float loc_key[RT_STACK_TOTAL - RT_STACK_SHARED];
+  float loc_key[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
   // lane state
-  enum { IDLE = 0, NODE = 1, LEAF = 2, DONE = 3 };
-  int st = IDLE;  // NODE: at internal node `cur`; LEAF: parked with leaf children; DONE: result ready to be written
-  bool anyhit = false, want_key = true, fallback = false, incons = false;
-  unsigned r = 0, cur = 0, pend0 = 0, pend1 = 0; int sp = 0, best = -1;
+  enum { IDLE = 0, ACTIVE = 1, DONE = 2 };  // ACTIVE: at `cur`; DONE: result ready to be written
+  enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };
+  int st = IDLE;
+  unsigned fl = 0u, r = 0, cur = 0; int sp = 0, best = -1;
   V3 o = mk3(0, 0, 0), d = mk3(0, 0, 0), inv = mk3(0, 0, 0);
-  float tlimit = 0.f, tmax = 0.f, pe0 = 0.f, pe1 = 0.f, omk = 0.f;
+  float tlimit = 0.f, tmax = 0.f, omk = 0.f;
   // exact lane, closest-hit rays: tcull = max(tmax, entry distance of the best hit's own leaf box) is what culling
   // compares with, t2 = smallest accepted distance among the tested primitives other than the best (see below)
   float tcull = 0.f, t2 = 0.f;
@@ -304,7 +312,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
   do {                                                                                                            \
     if (sp < RT_STACK_SHARED) { s_ref[sp][tid] = (ref_); if (!SUN) s_key[sp][tid] = (key_); sp++; }               \
     else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); if (!SUN) loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
-    else fallback = true; /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
+    else { fl |= F_FALLBACK; st = DONE; } /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
   } while (0)
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
 // box on its path is entered before the reference's running tmax at that moment.  Entry distances grow down a
@@ -315,36 +323,41 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
 // distance among tested candidates other than the current best (a replaced best included).  A candidate that was
 // never tested was culled with key > 1.000001 * max(t_b, e_b) of the best b of that moment: if b = m then
 // t_c > e_m; if b != m then t_c > t_b >= t2.  So t2 > e_m proves the claim; otherwise the ray goes to fb_list.
-#define RT_LEAF_TEST(ref_, e_)                                                                                    \
+#define RT_LEAF_TEST(ref_)                                                                                        \
   do {                                                                                                            \
     if (COUNT) n_leaves++;                                                                                        \
     float th_;                                                                                                    \
     if (rt_prim_test(sc.sorted_tv, ref_, o, d, th_) && th_ > 1e-6f) { /* bvh_traversal.cu:80-86 */               \
+      const bool anyhit_ = SUN || (fl & F_ANYHIT);                                                                \
       bool take_ = th_ < tmax;                                                                                    \
-      if (!anyhit && th_ == tmax && best >= 0 && ((ref_) & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take_ = true; \
+      if (!anyhit_ && th_ == tmax && best >= 0 && ((ref_) & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take_ = true; \
       if (take_) {                                                                                                \
-        if (EXACT && want_key) {                                                                                  \
-          if (anyhit) { if (!((e_) < th_)) fallback = true; } /* bulb shadow ray: first consistent occluder */    \
+        if (EXACT && !SUN && (fl & F_WANTKEY)) {                                                                  \
+          /* entry distance of the leaf's own box, with the exact test's arithmetic (third sector of the record) */ \
+          float4 b0_, b1_; rt_ld256(sc.sorted_tv + RT_TV_STRIDE * (size_t)((ref_) & RT_LEAF_MASK) + 4, b0_, b1_);  \
+          float e_; rt_slab<true>(b0_, b1_, o, inv, INFINITY, e_);                                                \
+          const bool cons_ = e_ < th_;                                                                            \
+          if (anyhit_) { if (!cons_) fl |= F_FALLBACK; } /* bulb shadow ray: first consistent occluder */         \
           else {                                                                                                  \
             if (best >= 0) t2 = fminf(t2, tmax);                                                                  \
-            incons = !((e_) < th_); tcull = incons ? fmaxf(th_, (e_)) : th_;                                      \
+            fl = cons_ ? (fl & ~F_INCONS) : (fl | F_INCONS); tcull = cons_ ? th_ : fmaxf(th_, e_);                \
           }                                                                                                       \
-        }                                                                                                         \
+        } else tcull = th_;                                                                                       \
         tmax = th_; best = (int)((ref_) & ~RT_LEAF_BIT);                                                          \
-        if (!(EXACT && want_key && !anyhit)) tcull = th_;                                                         \
-      } else if (EXACT && !anyhit) t2 = fminf(t2, th_);                                                           \
+      } else if (EXACT && !SUN && !anyhit_) t2 = fminf(t2, th_);                                                  \
     }                                                                                                             \
   } while (0)
 
   while (true) {
+    bool act = st == ACTIVE, atleaf = act && (cur & RT_LEAF_BIT);
+    unsigned actm = __ballot_sync(0xffffffffu, act), leafm = __ballot_sync(0xffffffffu, atleaf);
     // ---- retire finished rays and refill from the warp's chunk, RT_REFILL_MIN lanes at a time ----
-    unsigned leafm = __ballot_sync(0xffffffffu, st == LEAF), nodem = __ballot_sync(0xffffffffu, st == NODE);
-    const unsigned free_m = ~(leafm | nodem);
-    if (free_m && (__popc(free_m) >= RT_REFILL_MIN || free_m == 0xffffffffu)) {
+    const unsigned free_m = ~actm;
+    if (free_m && (__popc(free_m) >= RT_REFILL_MIN || actm == 0u)) {
       if (st == DONE) {
-        if (EXACT && (fallback || (incons && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;
+        if (EXACT && ((fl & F_FALLBACK) || ((fl & F_INCONS) && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;
         else {
-          const RtHit h = rt_finish_with_planes(sc, o, d, tlimit, anyhit, tmax, best);
+          const RtHit h = rt_finish_with_planes(sc, o, d, tlimit, SUN || (fl & F_ANYHIT), tmax, best);
           __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
         }
         st = IDLE;
@@ -364,42 +377,40 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
             r = chunk_next + rank;
             const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
             o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
-            anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
+            const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
             omk = 4e-7f * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
-            tmax = tlimit; tcull = tlimit; t2 = INFINITY; best = -1; fallback = false; incons = false; sp = 0; cur = (unsigned)sc.root; pend1 = 0u;
-            want_key = !SUN && !(anyhit && tlimit == INFINITY);  // a sun ray never culls by distance
-            st = NODE;
-            if (sc.n <= 0) st = DONE;                                                    // planes only
-            else if (cur & RT_LEAF_BIT) { pend0 = cur; pe0 = -INFINITY; st = LEAF; }     // single primitive: the root is the leaf
+            tmax = tlimit; tcull = tlimit; t2 = INFINITY; best = -1; sp = 0; cur = (unsigned)sc.root;
+            // a sun ray never culls by distance (tcull stays +INF) and needs no certificate
+            fl = (anyhit ? F_ANYHIT : 0u) | ((!SUN && !(anyhit && tlimit == INFINITY)) ? F_WANTKEY : 0u);
+            st = sc.n > 0 ? ACTIVE : DONE;  // n == 0: planes only.  n == 1: the root is the leaf
           }
           chunk_next += take;
         }
       }
-      leafm = __ballot_sync(0xffffffffu, st == LEAF); nodem = __ballot_sync(0xffffffffu, st == NODE);
-      if ((leafm | nodem) == 0u) {   // everybody was retired and nothing came in
+      act = st == ACTIVE; atleaf = act && (cur & RT_LEAF_BIT);
+      actm = __ballot_sync(0xffffffffu, act); leafm = __ballot_sync(0xffffffffu, atleaf);
+      if (actm == 0u) {  // everybody was retired and nothing came in
         if (exhausted) break;
         continue;
       }
     }
     bool need_pop = false;
-    if (__popc(leafm) >= RT_LEAF_MIN || nodem == 0u) {
+    if (__popc(leafm) >= RT_LEAF_MIN || leafm == actm) {
       // ---- leaf phase ----
-      if (st == LEAF) {
-        if (pend0) RT_LEAF_TEST(pend0, pe0);
-        if (pend1 && !(anyhit && best >= 0)) RT_LEAF_TEST(pend1, pe1);
-        pend0 = pend1 = 0u;
-        if ((anyhit && best >= 0) || fallback) st = DONE; else need_pop = true;
+      if (atleaf) {
+        RT_LEAF_TEST(cur);
+        if (((SUN || (fl & F_ANYHIT)) && best >= 0) || (fl & F_FALLBACK)) st = DONE; else need_pop = true;
       }
-    } else if (st == NODE) {
+    } else if (act && !atleaf) {
       // ---- node phase ----
       if (COUNT) n_nodes++;
       const float4* np = sc.nodes + 4 * (size_t)cur;
       float4 l0, l1, r0, r1;
       rt_ld256(np, l0, l1); rt_ld256(np + 2, r0, r1);
       float el, er;
-      // exact lane: order-independent part of the box test here, distance part below; otherwise the full inclusive test
       V3 tnl, tnr;
+      // exact lane: order-independent part of the box test here, distance part below; otherwise the full inclusive test
       bool hl = rt_slab_tn<true>(l0, l1, o, inv, (EXACT || SUN) ? INFINITY : tmax, el, tnl);
       bool hr = rt_slab_tn<true>(r0, r1, o, inv, (EXACT || SUN) ? INFINITY : tmax, er, tnr);
       const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
@@ -411,37 +422,24 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_near_kernel(const Rt
         const float tcut = tcull * 1.000001f;  // rounding of the products
         hl = hl && !(kl > tcut); hr = hr && !(kr > tcut);
       }
-      // One straight-line decision (selects, one push site) instead of a branch per case:
-      //  * leaf children are parked, nearer first; the internal child beside them (at most one) goes on the stack;
-      //  * two internal children: continue with the nearer, push the other;  one: continue with it;  none: pop.
-      const bool leafl = (refl & RT_LEAF_BIT) != 0u, leafr = (refr & RT_LEAF_BIT) != 0u;
-      const bool ll = hl && leafl, lr = hr && leafr, il = hl && !leafl, ir = hr && !leafr;
-      const bool near_r = er < el;
-      const bool both_i = il && ir, any_l = ll || lr, any_i = il || ir;
-      const bool sw_l = ll && lr && near_r, first_l = ll && !sw_l;
-      pend0 = any_l ? (first_l ? refl : refr) : 0u; pe0 = first_l ? el : er;
-      pend1 = (ll && lr) ? (sw_l ? refl : refr) : 0u; pe1 = sw_l ? el : er;
-      const bool take_r = both_i ? near_r : ir;
-      const bool push_do = any_l ? any_i : both_i;
-      const bool push_r = any_l ? ir : !near_r;
-      if (push_do) RT_PUSH(push_r ? refr : refl, push_r ? kr : kl);
-      cur = take_r ? refr : refl;
-      st = any_l ? LEAF : NODE;
-      need_pop = !any_l && !any_i;
-      if (fallback) { st = DONE; need_pop = false; }  // stack overflow: the reference-order pass decides
+      // nearer hit child next (leaf or not), the other one on the stack
+      const bool right_first = hr && (!hl || er < el);
+      if (hl && hr) RT_PUSH(right_first ? refl : refr, right_first ? kl : kr);
+      cur = right_first ? refr : refl;
+      need_pop = !(hl || hr);
     }
-    // ---- next node from the stack, skipping entries the current hit has made unreachable ----
+    // ---- next position from the stack, skipping entries the current hit has made unreachable ----
     if (need_pop) {
       st = DONE;
       if (SUN) {
-        if (sp > 0) { sp--; cur = sp < RT_STACK_SHARED ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; }
+        if (sp > 0) { sp--; cur = sp < RT_STACK_SHARED ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; }
       } else {
         const float tcut = EXACT ? tcull * 1.000001f : tmax;
         while (sp > 0) {
           sp--;
           const bool in_sh = sp < RT_STACK_SHARED;
           const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
-          if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = NODE; break; }
+          if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; break; }
         }
       }
     }
