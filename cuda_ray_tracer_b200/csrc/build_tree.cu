@@ -42,13 +42,13 @@ struct Delta {
 __device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref, float slack) {
   float4* h = nodes + 4 * (size_t)slot + 2 * side;
   const float cmax = fmaxf(fmaxf(fmaxf(fabsf(b.xmin), fabsf(b.xmax)), fmaxf(fabsf(b.ymin), fabsf(b.ymax))), fmaxf(fabsf(b.zmin), fabsf(b.zmax)));
-  __stcg(h, make_float4(b.xmin, b.ymin, b.zmin, b.xmax));
-  __stcg(h + 1, make_float4(b.ymax, b.zmax, __uint_as_float(ref), slack + 4e-7f * cmax));
+  __stcg(h, make_float4(b.xmin, b.ymin, b.xmax, b.ymax));
+  __stcg(h + 1, make_float4(b.zmin, b.zmax, __uint_as_float(ref), slack + 4e-7f * cmax));
 }
 __device__ inline float load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
   const float4* h = nodes + 4 * (size_t)slot + 2 * side;
   float4 u = __ldcg(h), v = __ldcg(h + 1);
-  b.xmin = u.x; b.ymin = u.y; b.zmin = u.z; b.xmax = u.w; b.ymax = v.x; b.zmax = v.y;
+  b.xmin = u.x; b.ymin = u.y; b.xmax = u.z; b.ymax = u.w; b.zmin = v.x; b.zmax = v.y;
   return v.w;
 }
 __device__ inline RtBox union_box(const RtBox& l, const RtBox& r) {  // AABB(left,right), interval.cuh:83-88
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   {
     float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
     rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
-    rec[4] = make_float4(box.xmin, box.ymin, box.zmin, box.xmax); rec[5] = make_float4(box.ymax, box.zmax, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.xmax, box.ymax); rec[5] = make_float4(box.zmin, box.zmax, 0.f, 0.f);
   }
   float slack = c.y;  // hit slack of the primitive, computed with the triangle setup (scene.cu, build.cuh)
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   {
     float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
     rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
-    rec[4] = make_float4(box.xmin, box.ymin, box.zmin, box.xmax); rec[5] = make_float4(box.ymax, box.zmax, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.xmax, box.ymax); rec[5] = make_float4(box.zmin, box.zmax, 0.f, 0.f);
   }
   float slack = c.y;  // hit slack of the primitive, computed with the triangle setup (scene.cu, build.cuh)
   uint32_t ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
@@ -219,7 +219,7 @@ __global__ void export_nodes_kernel(const float4* nodes, int n, int root, const 
     if (ref & RT_LEAF_BIT) { idx = (uint32_t)(n - 1) + (ref & RT_LEAF_MASK); o.prim = ref & RT_LEAF_MASK; o.nleaf = 1; }
     else { idx = (uint32_t)(karras ? karras[ref] : (int)ref); }
     child_idx[side] = idx;
-    float bb[6] = {u.x, u.w, u.y, v.x, u.z, v.y};  // xmin,xmax,ymin,ymax,zmin,zmax
+    float bb[6] = {u.x, u.z, u.y, u.w, v.x, v.y};  // xmin,xmax,ymin,ymax,zmin,zmax
     if (ref & RT_LEAF_BIT) { for (int q = 0; q < 6; q++) o.bbox[q] = bb[q]; out[idx] = o; }
     else { for (int q = 0; q < 6; q++) out[idx].bbox[q] = bb[q]; }
   }

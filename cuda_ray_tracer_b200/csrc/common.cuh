@@ -8,10 +8,11 @@
 //   prim_mat [n][3] float4  Materials (11 floats + pad), file order
 //   sorted_tv[n][6] float4  prim_tv gathered into Morton order (leaf k reads record k), 96-byte records:
 //                            the three prim_tv words + (file-order index, 0, 0, 0) | the leaf's own AABB in node-half
-//                            layout (xmin ymin zmin xmax | ymax zmax 0 0): read only when a hit is accepted, for the
+//                            layout (xmin ymin xmax ymax | zmin zmax 0 0): read only when a hit is accepted, for the
 //                            exact lane's certificate (traverse.cuh)
 //   nodes    [n-1][4] float4 64-byte internal node = two 32-byte child halves
-//                            half: min.xyz max.x | max.yz ref aux      (ref<0: leaf, see below)
+//                            half: xmin ymin xmax ymax | zmin zmax ref aux   (ref<0: leaf, see below); the pairs
+//                            (xmin,ymin) (xmax,ymax) (zmin,zmax) feed the packed f32x2 slab test (traverse.cuh)
 // Everything the tracer touches is indexed by file-order primitive index or by sorted position;
 // the reference's (type,id) PrimitiveReference pairs survive only for rt_export_reference_layout.
 #pragma once
