@@ -37,13 +37,14 @@ struct Delta {
   }
 };
 
-// aux = hit slack of the subtree (build.cuh, rt_leaf_slack) + 4e-7 * largest |coordinate| of the box: the
-// amount by which the traversal inflates the box before it culls the subtree by distance (traverse.cuh)
+// aux = (hit slack of the subtree (build.cuh, rt_leaf_slack) + 4e-7 * largest |coordinate| of the box) * 1.000001:
+// the amount by which the traversal inflates the box before it culls the subtree by distance, with the rounding
+// allowance of its key already applied (traverse.cuh, rt_key_inflated)
 __device__ inline void store_half(float4* nodes, int slot, int side, const RtBox& b, uint32_t ref, float slack) {
   float4* h = nodes + 4 * (size_t)slot + 2 * side;
   const float cmax = fmaxf(fmaxf(fmaxf(fabsf(b.xmin), fabsf(b.xmax)), fmaxf(fabsf(b.ymin), fabsf(b.ymax))), fmaxf(fabsf(b.zmin), fabsf(b.zmax)));
   __stcg(h, make_float4(b.xmin, b.ymin, b.xmax, b.ymax));
-  __stcg(h + 1, make_float4(b.zmin, b.zmax, __uint_as_float(ref), slack + 4e-7f * cmax));
+  __stcg(h + 1, make_float4(b.zmin, b.zmax, __uint_as_float(ref), (slack + 4e-7f * cmax) * 1.000001f));
 }
 __device__ inline float load_half_box(const float4* nodes, int slot, int side, RtBox& b) {
   const float4* h = nodes + 4 * (size_t)slot + 2 * side;

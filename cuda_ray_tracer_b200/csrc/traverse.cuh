@@ -157,13 +157,13 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
 // 4e-7 terms the rounding of t*d + o inside the primitive test.
 // Per axis the inflated slab is entered at tn - S/|d| in real arithmetic.  tn (the exact test's own near
 // distance, fl(fl(b - o) * inv)) carries a relative error of at most 3 ulp, inv = fl(1/d) half an ulp, so
-// key = fma(-S * 1.000001, |inv|, tn) satisfies key <= t * (1 + 3e-7) for every accepted hit t of the subtree;
+// key = fma(-S * 1.000001, |inv|, tn) (the factor is folded into the stored aux and into omk) satisfies key <= t * (1 + 3e-7) for every accepted hit t of the subtree;
 // the caller compares it with tmax * 1.000001.  Rounding is monotone, so key <= tn: the inflated test never
 // culls more than the exact one.  Axis-parallel rays (inv = +-INF): tn is -INF inside the slab (key -INF),
 // +INF outside (key NaN, dropped by fmaxf: no constraint from that axis, and the exact test fails anyway).
 __device__ __forceinline__ float rt_key_inflated(const V3 tn, const float aux, const V3 inv, const float omk) {
-  const float nS = -((aux + omk) * 1.000001f);
-  return fmaxf(fmaxf(__fmaf_rn(nS, fabsf(inv.x), tn.x), __fmaf_rn(nS, fabsf(inv.y), tn.y)), __fmaf_rn(nS, fabsf(inv.z), tn.z));
+  const float S = aux + omk;  // both already carry the factor 1.000001 (build_tree.cu store_half; ray fetch)
+  return fmaxf(fmaxf(__fmaf_rn(-S, fabsf(inv.x), tn.x), __fmaf_rn(-S, fabsf(inv.y), tn.y)), __fmaf_rn(-S, fabsf(inv.z), tn.z));
 }
 
 struct RtStack {  // per-thread traversal stack: first RT_STACK_SHARED entries in shared memory, the rest in local memory
@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
   RtRay2 q2 = rt_ray2(d, d);  // origin and reciprocal direction live only as the packed pairs of the slab test
   // exact lane, closest-hit rays: tcull = max(tmax, entry distance of the best hit's own leaf box) is what culling
   // compares with, t2 = smallest accepted distance among the tested primitives other than the best (see below)
-  float tcull = 0.f, t2 = 0.f;
+  float tcull = 0.f, t2 = 0.f, tcut = 0.f;  // tcut = tcull * 1.000001 (rounding of the key's products), kept in step
   // warp state (uniform)
   unsigned chunk_next = 0, chunk_end = 0; bool exhausted = false;
 
@@ -377,6 +377,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
             fl = cons_ ? (fl & ~F_INCONS) : (fl | F_INCONS); tcull = cons_ ? th_ : fmaxf(th_, e_);                \
           }                                                                                                       \
         } else tcull = th_;                                                                                       \
+        tcut = tcull * 1.000001f;                                                                                 \
         tmax = th_; best = (int)((ref_) & ~RT_LEAF_BIT);                                                          \
       } else if (EXACT && !SUN && !anyhit_) t2 = fminf(t2, th_);                                                  \
     }                                                                                                             \
@@ -413,9 +414,9 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
             const V3 o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
             const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
-            omk = 4e-7f * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+            omk = (4e-7f * 1.000001f) * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
             q2 = rt_ray2(o, inv);
-            tmax = tlimit; tcull = tlimit; t2 = INFINITY; best = -1; sp = 0; cur = (unsigned)sc.root;
+            tmax = tlimit; tcull = tlimit; tcut = tlimit * 1.000001f; t2 = INFINITY; best = -1; sp = 0; cur = (unsigned)sc.root;
             // a sun ray never culls by distance (tcull stays +INF) and needs no certificate
             fl = (anyhit ? F_ANYHIT : 0u) | ((!SUN && !(anyhit && tlimit == INFINITY)) ? F_WANTKEY : 0u);
             st = sc.n > 0 ? ACTIVE : DONE;  // n == 0: planes only.  n == 1: the root is the leaf
@@ -455,7 +456,6 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
         // (sun shadow rays: tcull stays +INF, nothing is culled by distance)
         const V3 inv = rt_ray2_inv(q2);
         kl = rt_key_inflated(tnl, l1.w, inv, omk); kr = rt_key_inflated(tnr, r1.w, inv, omk);
-        const float tcut = tcull * 1.000001f;  // rounding of the products
         hl = hl && !(kl > tcut); hr = hr && !(kr > tcut);
       }
       // nearer hit child next (leaf or not), the other one on the stack
@@ -470,12 +470,12 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       if (SUN) {
         if (sp > 0) { sp--; cur = sp < RT_STACK_SHARED ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; }
       } else {
-        const float tcut = EXACT ? tcull * 1.000001f : tmax;
+        const float tpop = EXACT ? tcut : tmax;
         while (sp > 0) {
           sp--;
           const bool in_sh = sp < RT_STACK_SHARED;
           const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
-          if (!(key > tcut)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; break; }
+          if (!(key > tpop)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; break; }
         }
       }
     }
