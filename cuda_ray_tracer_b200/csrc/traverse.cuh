@@ -320,13 +320,14 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
                                                                        const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
                                                                        unsigned* fb_count) {
-  __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
-  __shared__ float s_key[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
+  // stack entry = (reference, culling key): one 64-bit shared-memory access per push / pop (SUN: references only)
+  __shared__ unsigned s_ref[SUN ? RT_STACK_SHARED : 1][RT_TRAV_THREADS];
+  __shared__ uint2 s_ent[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
   const unsigned lane = threadIdx.x & 31;
   const int tid = threadIdx.x;
   unsigned long long n_nodes = 0, n_leaves = 0;
-  unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
-  float loc_key[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
+  unsigned loc_ref[SUN ? RT_STACK_TOTAL - RT_STACK_SHARED : 1];
+  uint2 loc_ent[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
   // lane state
   enum { IDLE = 0, ACTIVE = 1, DONE = 2 };  // ACTIVE: at `cur`; DONE: result ready to be written
   enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };
@@ -343,8 +344,8 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
 
 #define RT_PUSH(ref_, key_)                                                                                       \
   do {                                                                                                            \
-    if (sp < RT_STACK_SHARED) { s_ref[sp][tid] = (ref_); if (!SUN) s_key[sp][tid] = (key_); sp++; }               \
-    else if (sp < RT_STACK_TOTAL) { loc_ref[sp - RT_STACK_SHARED] = (ref_); if (!SUN) loc_key[sp - RT_STACK_SHARED] = (key_); sp++; } \
+    if (sp < RT_STACK_SHARED) { if (SUN) s_ref[sp][tid] = (ref_); else s_ent[sp][tid] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
+    else if (sp < RT_STACK_TOTAL) { if (SUN) loc_ref[sp - RT_STACK_SHARED] = (ref_); else loc_ent[sp - RT_STACK_SHARED] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
     else { fl |= F_FALLBACK; st = DONE; } /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
   } while (0)
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
@@ -473,9 +474,8 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
         const float tpop = EXACT ? tcut : tmax;
         while (sp > 0) {
           sp--;
-          const bool in_sh = sp < RT_STACK_SHARED;
-          const float key = in_sh ? s_key[sp][tid] : loc_key[sp - RT_STACK_SHARED];
-          if (!(key > tpop)) { cur = in_sh ? s_ref[sp][tid] : loc_ref[sp - RT_STACK_SHARED]; st = ACTIVE; break; }
+          const uint2 e = sp < RT_STACK_SHARED ? s_ent[sp][tid] : loc_ent[sp - RT_STACK_SHARED];
+          if (!(__uint_as_float(e.y) > tpop)) { cur = e.x; st = ACTIVE; break; }
         }
       }
     }
