@@ -204,7 +204,10 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
       uint32_t v[5], d, out[5];
       xw_seed(1234ull + (unsigned long long)pix, v, d);
       if (s == 0) { for (int k = 0; k < 5; k++) out[k] = v[k]; }
-      else if (s == s0) xw_matvec_nib_lowseed(s_nib, v, out);  // 1234 + pix < 2^32
+      else if (s == s0) {  // 1234 + pix < 2^32
+        if (P.rng_live || P.cam.dof_focus != 0.0f) xw_matvec_nib_lowseed<true>(s_nib, v, out);
+        else xw_matvec_nib_lowseed<false>(s_nib, v, out);  // only the two jitter draws will ever read this state
+      }
       else xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);  // block straddling two sample indices
       rng.v0 = out[0]; rng.v1 = out[1]; rng.v2 = out[2]; rng.v3 = out[3]; rng.v4 = out[4]; rng.d = d;
       const float jx = xw_rand(-0.5f, 0.5f, rng);  // draw.cu:165-169
@@ -308,7 +311,15 @@ __device__ __forceinline__ V3 rough_offset(float rough, Xorwow& rng, int zyx) {
   return mk3(a, b, c);
 }
 
-__global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
+// The kernel waits on three dependent random loads per ray (hit -> leaf record -> material), so what it needs is
+// many warps in flight: 64 registers (8 CTAs of 128 threads per SM; 118 registers and 17 % occupancy without the
+// bound), and a FULL = false instantiation for scenes without mirrors, glass or GI, where the continuation stack
+// never holds a pending call and half of the state machine is dead code.
+#ifndef RT_SHADE_MIN_CTAS
+#define RT_SHADE_MIN_CTAS 8
+#endif
+template <bool FULL>
+__global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
                                                    const float4* __restrict__ qin, const unsigned n_front, const unsigned n_back,
                                                    float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
   const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -377,7 +388,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
         acc.x += df_w.x * er; acc.y += df_w.y * eg; acc.z += df_w.z * eb;
       }
       li++;
-    } else if (type == T_W_REFRACT1) {
+    } else if (FULL && type == T_W_REFRACT1) {
       // refractionLight after the inside ray, draw.cu:484-495 (a miss leaves the default ObjectInfo)
       V3 normal = mk3(0.f, 0.f, 0.f), ip = mk3(0.f, 0.f, 0.f); float ior = 1.458f;
       if (hid != -1) {
@@ -404,7 +415,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
         }
       }
       if (hid == -1) {
-        if (type == T_W_REFLECT && flag) sp--;  // the provisional refract(outer) frame is never evaluated
+        if (FULL && type == T_W_REFLECT && flag) sp--;  // the provisional refract(outer) frame is never evaluated
       } else {
         SurfHit h; reconstruct_hit(sc, hid, ht, o, d, h);
         if (type == T_W_PRIMARY) { NEED_ACC(); acc.w = 1.0f; }  // color.a = 1, draw.cu:281
@@ -415,7 +426,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
         const V3 w_refr = mul3(Wt, mul3(ms, h.trans));
         const bool shiny = !rgb_is_zero(h.shin), transp = !rgb_is_zero(h.trans);
         // frames are pushed in reverse evaluation order: gi, refract, reflect, then diffuse runs now
-        if ((type == T_W_PRIMARY || type == T_W_GI) && P.cam.gi != 0) {
+        if (FULL && (type == T_W_PRIMARY || type == T_W_GI) && P.cam.gi != 0) {
           const int g = type == T_W_PRIMARY ? P.cam.gi : b;
           if (sp < P.depth) {
             const V3 wg = mul3(w_diff, h.color);
@@ -425,9 +436,9 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
             sp++;
           } else overflow = true;
         }
-        if (type == T_W_REFLECT) {
+        if (FULL && type == T_W_REFLECT) {
           if (flag) { const float4 t0 = FR(sp - 1, 0); FR(sp - 1, 0) = make_float4(t0.x, w_refr.x, w_refr.y, w_refr.z); }
-        } else if (transp && b > 0) {
+        } else if (FULL && transp && b > 0) {
           if (sp < P.depth) {
             FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_REFRACT, b, 0u)), w_refr.x, w_refr.y, w_refr.z);
             FR(sp, 1) = make_float4(d.x, d.y, d.z, h.point.x);
@@ -436,7 +447,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
             sp++;
           } else overflow = true;
         }
-        if (shiny && b > 0) {
+        if (FULL && shiny && b > 0) {
           if (sp < P.depth) {
             FR(sp, 0) = make_float4(__uint_as_float(hdr_pack(T_REFLECT, b, transp ? 1u : 0u)), w_refl.x, w_refl.y, w_refl.z);
             FR(sp, 1) = make_float4(d.x, d.y, d.z, h.point.x);
@@ -483,7 +494,7 @@ __global__ void __launch_bounds__(128) shade_kernel(const RenderParams P, const 
         in_diffuse = false;
         continue;
       }
-      if (sp == 0) break;  // sample finished
+      if (!FULL || sp == 0) break;  // sample finished (without mirrors, glass or GI nothing is ever pending)
       sp--;
       const float4 g0 = FR(sp, 0);
       const unsigned gh = __float_as_uint(g0.x);
@@ -922,7 +933,8 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
                                      rs->counters, rs->stats, B.fb_list);
       launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
-      shade_kernel<<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+      if (s->any_shiny || s->any_trans || s->cfg.gi != 0) shade_kernel<true><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+      else shade_kernel<false><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
       launches++;
       RT_CUDA(cudaGetLastError());
       RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 20, cudaMemcpyDeviceToHost, st));

@@ -76,6 +76,9 @@ __device__ __forceinline__ void xw_matvec(const uint32_t* __restrict__ M, const 
 // Seeds below 2^32 (1234 + pixel always is) leave state words v2, v3 of xw_seed independent of the seed, so their
 // share of the product is one constant vector per matrix (tab[RT_RNG_NIB_WORDS .. +5), written by the table
 // kernel) and only the 24 nibbles of v0, v1, v4 are looked up.
+// ALL = false: only words 0, 1 and 4 of the result, which is all that the first two draws read (xw_next consumes
+// v0 and v4, then what was v1): enough when nothing but the pixel jitter is ever drawn from this state.
+template <bool ALL>
 __device__ __forceinline__ void xw_matvec_nib_lowseed(const uint32_t* tab, const uint32_t* in, uint32_t* out) {
   uint32_t r0 = tab[RT_RNG_NIB_WORDS], r1 = tab[RT_RNG_NIB_WORDS + 1], r2 = tab[RT_RNG_NIB_WORDS + 2], r3 = tab[RT_RNG_NIB_WORDS + 3],
            r4 = tab[RT_RNG_NIB_WORDS + 4];
@@ -86,7 +89,7 @@ __device__ __forceinline__ void xw_matvec_nib_lowseed(const uint32_t* tab, const
 #pragma unroll
     for (int j = 0; j < 8; j++) {
       const uint32_t* e = tab + ((i * 8 + j) * 16 + ((w >> (4 * j)) & 15u)) * 5;
-      r0 ^= e[0]; r1 ^= e[1]; r2 ^= e[2]; r3 ^= e[3]; r4 ^= e[4];
+      r0 ^= e[0]; r1 ^= e[1]; if (ALL) { r2 ^= e[2]; r3 ^= e[3]; } r4 ^= e[4];
     }
   }
   out[0] = r0; out[1] = r1; out[2] = r2; out[3] = r3; out[4] = r4;
