@@ -41,6 +41,7 @@ struct RenderParams {
   int slot0, npix, S;   // this pass: pixel slots [slot0, slot0+npix), S = npix * spp samples
   int depth;        // continuation stack depth (frames per sample)
   int ref_order /* traversal lane, RT_LANE_* */, rough_zyx, need_rng;
+  int full_shade;   // mirrors, glass or GI present: the continuation stack can hold pending calls (shade_kernel<true>)
   int rng_live;     // something after generate draws random numbers (rough materials, gi): the state is stored
   int num_lights;
 };
@@ -126,6 +127,35 @@ __device__ __forceinline__ void queue_append(float4* __restrict__ q, uint32_t* c
   }
 }
 
+// The same with ONE atomic per block and queue end: a single counter serialises in L2 at roughly a nanosecond per
+// atomic, which at one atomic per warp was the whole run time of generate_kernel (56 % of its stall samples).
+// Every thread of the block must call it; s_tmp holds 2 * WARPS + 2 words.
+template <int WARPS>
+__device__ __forceinline__ void queue_append_block(float4* __restrict__ q, uint32_t* count_front, uint32_t* count_back, unsigned cap, bool has,
+                                                   V3 o, V3 d, float tlimit, unsigned tag, unsigned* s_tmp) {
+  const bool back = has && (tag & RT_RAY_ANYHIT) && tlimit == INFINITY;
+  const unsigned mf = __ballot_sync(0xffffffffu, has && !back), mb = __ballot_sync(0xffffffffu, back);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, below = (1u << lane) - 1u;
+  if (lane == 0) { s_tmp[warp] = (unsigned)__popc(mf); s_tmp[WARPS + warp] = (unsigned)__popc(mb); }
+  __syncthreads();
+  if (threadIdx.x == 0 || threadIdx.x == 32) {
+    const unsigned* c = s_tmp + (threadIdx.x ? WARPS : 0);
+    unsigned tot = 0;
+    for (int w = 0; w < WARPS; w++) tot += c[w];
+    s_tmp[2 * WARPS + (threadIdx.x ? 1 : 0)] = tot ? atomicAdd(threadIdx.x ? count_back : count_front, tot) : 0u;
+  }
+  __syncthreads();
+  if (has) {
+    const unsigned* c = s_tmp + (back ? WARPS : 0);
+    unsigned pre = s_tmp[2 * WARPS + (back ? 1 : 0)];
+    for (unsigned w = 0; w < warp; w++) pre += c[w];
+    const size_t r = back ? (size_t)cap - 1 - (pre + __popc(mb & below)) : (size_t)pre + __popc(mf & below);
+    q[2 * r] = make_float4(o.x, o.y, o.z, tlimit);
+    q[2 * r + 1] = make_float4(d.x, d.y, d.z, __uint_as_float(tag));
+  }
+  __syncthreads();  // s_tmp is reused by the caller's next round
+}
+
 // 4-bit lookup tables of the power matrices (rng.cuh: xw_matvec_nib), built once per table upload
 __global__ void rng_nibble_kernel(const uint32_t* __restrict__ mats, int count, uint32_t* __restrict__ nib) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -172,6 +202,7 @@ __global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams
 #define RT_GEN_CHUNKS 4   // a block generates 4 x 256 consecutive samples: the 12.8 KB skip-ahead table is staged once
 __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
   __shared__ uint32_t s_nib[RT_RNG_NIB_STRIDE];
+  __shared__ unsigned s_app[2 * 8 + 2];
   const long long base = (long long)blockIdx.x * (256 * RT_GEN_CHUNKS);
   // sample-major order (i = sample * npix + pixel slot): a block almost always lies inside one sample index,
   // whose skip-ahead matrix all its threads share
@@ -194,7 +225,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
   bool has = false; V3 eye = mk3(0, 0, 0), dir = mk3(0, 0, 0);
   if (i < P.S) {
     B.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    B.ctl[i] = 0u;
+    if (P.full_shade) B.ctl[i] = 0u;
   }
   if (live) {
     Xorwow rng; rng.v0 = rng.v1 = rng.v2 = rng.v3 = rng.v4 = rng.d = 0u; rng.bm_flag = 0u; rng.bm_extra = 0.f;
@@ -256,10 +287,10 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     if (C.bounces != 0) {  // hitNearest: a ray with bounce == 0 hits nothing (draw.cu:294)
       has = true;
       B.frames[(size_t)i] = make_float4(__uint_as_float(hdr_pack(T_W_PRIMARY, C.bounces, 0u)), 1.f, 1.f, 1.f);
-      B.ctl[i] = 1u;
+      if (P.full_shade) B.ctl[i] = 1u;
     } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
   }
-  queue_append(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, has, eye, dir, INFINITY, (unsigned)i);
+  queue_append_block<8>(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, has, eye, dir, INFINITY, (unsigned)i, s_app);
   }
 }
 
@@ -333,7 +364,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
     const float ht = hv.x; const int hid = __float_as_int(hv.y);
     const size_t S = (size_t)P.S;
     float4* const F = B.frames + i;  // frame slot (L,q) is F[(L*4+q)*S]
-    int sp = (int)B.ctl[i];
+    int sp = FULL ? (int)B.ctl[i] : 1;  // without mirrors, glass or GI exactly one frame is live while a ray is in flight
     Xorwow rng; bool rng_loaded = false, rng_dirty = false;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); bool acc_loaded = false, acc_dirty = false;
     bool overflow = false;
@@ -566,7 +597,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
         } else overflow = true;
       }
     }
-    B.ctl[i] = (unsigned)sp;
+    if (FULL) B.ctl[i] = (unsigned)sp;
     if (rng_dirty) rng_store(B, i, rng);
     if (acc_dirty) B.accum[i] = acc;
     if (overflow) B.counters[2] = 1u;
@@ -861,6 +892,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
   if (P.depth > 200) { rt_set_error("rt_render: bounces too large for the continuation stack"); return RT_ERR_INVALID; }
   P.rng_live = (s->any_rough || s->cfg.gi != 0) ? 1 : 0;
+  P.full_shade = (s->any_shiny || s->any_trans || s->cfg.gi != 0) ? 1 : 0;
   P.need_rng = (P.mode != 0) || s->cfg.dof_focus != 0.0f || s->any_rough || s->cfg.gi != 0;
   if (s->cfg.fisheye || s->cfg.panorama) { if (P.mode == 0 && !s->any_rough && s->cfg.gi == 0) P.need_rng = 0; }
   P.num_lights = s->cfg.num_suns + s->cfg.num_bulbs;
@@ -933,7 +965,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
                                      rs->counters, rs->stats, B.fb_list);
       launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
-      if (s->any_shiny || s->any_trans || s->cfg.gi != 0) shade_kernel<true><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+      if (P.full_shade) shade_kernel<true><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
       else shade_kernel<false><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
       launches++;
       RT_CUDA(cudaGetLastError());
