@@ -605,9 +605,10 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
 #undef NEED_RNG
 #undef NEED_ACC
   }
-  queue_append(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, emit, eo, ed, elimit, etag);
-  const unsigned sm = __ballot_sync(0xffffffffu, shaded);
-  if (sm && (threadIdx.x & 31) == 0) atomicAdd(B.stats + 2, (unsigned long long)__popc(sm));
+  __shared__ unsigned s_app[2 * 4 + 2];
+  queue_append_block<4>(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, emit, eo, ed, elimit, etag, s_app);
+  const int nshaded = __syncthreads_count(shaded);  // one atomic per block: a single hot counter serialises in L2
+  if (nshaded && threadIdx.x == 0) atomicAdd(B.stats + 2, (unsigned long long)nshaded);
 }
 
 // ---- resolve: sample sum in the butterfly order of render_kernel_warp_aa, sRGB, 8-bit store -----
