@@ -272,7 +272,7 @@ def run_b200(a):
     img_d = torch.zeros((Hh, W, 4), dtype=torch.uint8, device=dev)
     img_h = torch.zeros((Hh, W, 4), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    tiles = parallel.tile_set(world, rank)
+    tiles = parallel.tile_set(world, rank, width=W)
     rflags = api.SPP_TRUE | api.TIME_TRAVERSE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0)
     BUILD_LAUNCHES = 1 + 8  # update_tris + init, bounds, morton, 4 onesweep passes, bottom-up
 
@@ -342,6 +342,20 @@ def run_b200(a):
                        dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(alg, op=dist.ReduceOp.SUM)
+    # diagnostics for the scaling figure: per-rank render time of one frame (load balance) and the cost of the gather alone
+    diag = {}
+    if world > 1:
+        c2 = api.Counters()
+        sc.render_device(W, Hh, spp, img_d, flags=rflags, tiles=tiles, counters=c2)
+        t = torch.zeros(world, dtype=torch.float64, device=dev); t[rank] = c2.render_ms
+        dist.all_reduce(t)
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        parallel.gather_framebuffer(img_d, 0); torch.cuda.synchronize(); dist.barrier()
+        e0.record()
+        for _ in range(5):
+            parallel.gather_framebuffer(img_d, 0)
+        e1.record(); torch.cuda.synchronize()
+        diag = {"rank_render_ms": [round(x, 3) for x in t.tolist()], "gather_ms": e0.elapsed_time(e1) / 5}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -375,7 +389,7 @@ def run_b200(a):
         "data": "synthetic",
         "config": {"workload": workload_name(a), "lane": "near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)",
                    "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
-                   "parallelism": "scene replicated, image in interleaved 32x8 tiles over %d GPU(s), NCCL broadcast + framebuffer reduce" % world},
+                   "parallelism": "scene replicated, image in interleaved %dx%d tiles over %d GPU(s), NCCL broadcast + framebuffer reduce" % (parallel.tile_shape(world, W) + (world,))},
         "lbvh_build_ms": dev_res["build_ms"],
         "rays_per_step": dev_res["rays"] / a.steps,
         "nodes_per_ray": alg[1].item() / max(alg[3].item(), 1), "leaf_tests_per_ray": alg[2].item() / max(alg[3].item(), 1),
@@ -391,6 +405,8 @@ def run_b200(a):
                      "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test. The 64 MB of nodes and 96 MB of leaf records are served by L2 (92-96 % hit rate, DRAM traffic = rays in + hits out), so the rate can exceed the HBM copy peak; the bound that applies is the measured L2 rate for 64-byte random gathers (profiles/l2_peaks_r01.json, BASELINE.json's 'traversal roofline ... against L2 bandwidth')"},
         "clocks": sampler.summary(),
     }
+    if diag:
+        line["scaling_diag"] = diag
     if not a.no_cpu_baseline and world == 1:
         try:
             line["cpu_baseline"] = cpu_baseline(a, cfg, {"tri": [p0, p1, p2], "tri_mat": arrays["tri_mat"].cpu().numpy(),

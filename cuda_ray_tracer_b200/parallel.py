@@ -7,9 +7,32 @@ from . import api
 TILE_W, TILE_H = 32, 8
 
 
-def tile_set(world, rank, tile_w=TILE_W, tile_h=TILE_H):
+def tile_shape(world, width=None):
+    """256-pixel tile shape for `world` ranks.  Tile t (row-major) belongs to rank t % world, so when the number of
+    tiles per image row is a multiple of world every rank would own whole COLUMNS of tiles and the load would
+    follow the picture's horizontal structure (measured: 7 % spread at 8 GPUs on the 4K soup).  Pick the shape
+    whose tiles-per-row shares the fewest factors with world (ties: the squarest), e.g. 256x1 at 3840 wide:
+    15 tiles per row, rank = (tx - ty) mod 8, a diagonal pattern."""
+    if width is None or world <= 1:
+        return TILE_W, TILE_H
+    import math
+    best = None
+    for tw, th in ((32, 8), (64, 4), (16, 16), (128, 2), (256, 1)):
+        tx = (width + tw - 1) // tw
+        waste = tx * tw - width
+        key = (math.gcd(tx, world), waste, abs(math.log2(tw / th)))
+        if best is None or key < best[0]:
+            best = (key, (tw, th))
+    return best[1]
+
+
+def tile_set(world, rank, tile_w=None, tile_h=None, width=None):
     """rt_tile_set for `rank` of `world` (None for a single rank = whole image)"""
-    return api.TileSet(tile_w, tile_h, world, rank) if world > 1 else None
+    if world <= 1:
+        return None
+    if tile_w is None or tile_h is None:
+        tile_w, tile_h = tile_shape(world, width)
+    return api.TileSet(tile_w, tile_h, world, rank)
 
 
 def tile_owner(w, h, world, tile_w=TILE_W, tile_h=TILE_H):
