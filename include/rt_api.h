@@ -96,7 +96,7 @@ enum {
                                  hit sit just outside, and then the reference's answer depends on its
                                  visiting order.  The DEFAULT lane is also near-first but provably returns
                                  the reference's answer (slack-inflated culling + per-ray certificate +
-                                 reference-order fallback, DESIGN.md §6); this flag only removes that
+                                 reference-order fallback, DESIGN.md §4.2); this flag only removes that
                                  machinery, to measure what exactness costs                          */
   RT_ROUGH_ZYX        = 4u,   /* draw order of the three unsequenced standerdD() arguments
                                  (draw.cu:335-337): z,y,x instead of x,y,z                          */

@@ -330,3 +330,22 @@ def test_exact_lane_equals_reference_order_redchair_and_soup():
     assert c1.nodes_visited < 0.6 * c0.nodes_visited
     a0 = sc.render(640, 360, 0, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(640, 360, 0, 0, want_ids=True)
     assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"])
+
+
+def test_exact_lane_equals_reference_order_sphere_field():
+    """sphere fields of the named sizes (r = 0.25 * N^(-1/3)); 1M spheres, both key widths"""
+    n = 1_000_000
+    cfg, a = synth.spheres(n, seed=1, width=64, height=64, aa=0)
+    desc, keep = api.make_desc(cfg, a)
+    sc = api.Scene(desc, 0)
+    org, d = random_rays(1_000_000, 4, 1.5)
+    for bits in (30, 63):
+        sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED)
+        ri, rt_, _ = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER)
+        ei, et, c1 = gpu_trace(sc, org, d, api.COUNTERS)
+        assert np.array_equal(ei, ri) and np.array_equal(et.view(np.uint32), rt_.view(np.uint32)), "%d rays differ (%d bits)" % ((ei != ri).sum(), bits)
+        assert (ei >= 0).mean() > 0.2
+        a0 = sc.render(480, 270, 0, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(480, 270, 0, 0, want_ids=True)
+        assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"])
+    a2 = sc.render(240, 135, 16, api.SPP_TRUE | api.TRAVERSE_REF_ORDER); a3 = sc.render(240, 135, 16, api.SPP_TRUE)
+    assert np.array_equal(a2["rgba"], a3["rgba"]) and a2["counters"].rays == a3["counters"].rays
