@@ -52,6 +52,20 @@ def broadcast_scene(tensors, src=0):
             dist.broadcast(t, src)
 
 
+def upload_sharded(host_pinned, dev_full, dev_part, rank, world):
+    """host -> every GPU, for a replicated array that all ranks hold in pinned host memory: each rank copies only
+    its 1/world slice over its own PCIe link and NCCL all-gathers the slices over NVLink (36 MB of vertices at 8
+    GPUs: 4.5 MB of PCIe per rank instead of 36).  dev_full: [world * rows_per_rank, ...] device tensor (rows past the
+    array's length are padding), dev_part: [rows_per_rank, ...] staging.  Returns dev_full."""
+    import torch.distributed as dist
+    rows = dev_part.shape[0]
+    lo = rank * rows; hi = min(lo + rows, host_pinned.shape[0])
+    if hi > lo:
+        dev_part[: hi - lo].copy_(host_pinned[lo:hi], non_blocking=True)
+    dist.all_gather_into_tensor(dev_full, dev_part)
+    return dev_full
+
+
 def gather_framebuffer(img, dst=0):
     """sum the per-rank images onto rank `dst`: every rank wrote only its own tiles into a zeroed image, so the
     sum over uint8 is the gather (33 MB at 4K: tens of microseconds over NVLink)"""

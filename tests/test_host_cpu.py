@@ -181,6 +181,12 @@ img = torch.where((own == rank)[..., None], full, torch.zeros_like(full))   # th
 parallel.gather_framebuffer(img, 0)                        # framebuffer gather
 if rank == 0:
     assert torch.equal(img, full), "gathered framebuffer differs"
+# sharded upload: every rank contributes 1/world of a replicated host array, all-gather rebuilds it everywhere
+host = torch.arange(1001 * 3, dtype=torch.float32).reshape(1001, 3)
+rows = (1001 + world - 1) // world
+fullbuf = torch.zeros((rows * world, 3)); part = torch.zeros((rows, 3))
+parallel.upload_sharded(host, fullbuf, part, rank, world)
+assert torch.equal(fullbuf[:1001], host), "sharded upload differs"
 dist.barrier(); dist.destroy_process_group()
 sys.stdout.write("ok%d\n" % rank); sys.stdout.flush()
 '''
