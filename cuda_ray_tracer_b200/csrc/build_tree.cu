@@ -60,6 +60,16 @@ __device__ inline RtBox union_box(const RtBox& l, const RtBox& r) {  // AABB(lef
   return o;
 }
 
+// Arrival handshake of the bottom-up passes: one exchange with acquire-release ordering at device scope.  The
+// release half publishes this thread's 32-byte node half (written before it), the acquire half makes the sibling's
+// visible to the loads after it — the ordering the reference's refit lacks — without the two full
+// membar.gl fences (which on Blackwell also invalidate L1) that __threadfence() would cost per level.
+__device__ __forceinline__ int exch_acq_rel(int* addr, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(addr), "r"(v) : "memory");
+  return old;
+}
+
 // ---- fused bottom-up builder ------------------------------------------------------------------
 template <typename KeyT>
 __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ perm,
@@ -92,10 +102,8 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
     int s, side, mine;
     if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
     store_half(nodes, s, side, box, ref, slack);
-    __threadfence();
-    const int other = atomicExch(flags + s, mine);
+    const int other = exch_acq_rel(flags + s, mine);
     if (other == -1) return;  // sibling not there yet: it will finish this node
-    __threadfence();
     RtBox sib;
     slack = fmaxf(slack, load_half_box(nodes, s, side ^ 1, sib));
     if (side == 0) { r = other; box = union_box(box, sib); } else { l = other; box = union_box(sib, box); }
@@ -173,9 +181,7 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   while (true) {  // set_aabb_kernel_adapted, lbvh_builder.cu:353-386, plus the missing fences (F9)
     const int par = pi >> 1, side = pi & 1;
     store_half(nodes, par, side, box, ref, slack);
-    __threadfence();
-    if (atomicExch(counters + par, 1) == -1) return;  // counters were initialised to -1
-    __threadfence();
+    if (exch_acq_rel(counters + par, 1) == -1) return;  // counters were initialised to -1
     RtBox sib;
     slack = fmaxf(slack, load_half_box(nodes, par, side ^ 1, sib));
     box = side == 0 ? union_box(box, sib) : union_box(sib, box);
