@@ -223,7 +223,8 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     live = slot_to_pixel(P, P.slot0 + lp, x, y, pix);
   }
   bool has = false; V3 eye = mk3(0, 0, 0), dir = mk3(0, 0, 0);
-  if (i < P.S) {
+  // a sample that emits a primary ray is initialised by the first shade visit (shade_kernel<.., FIRST = true>)
+  if (i < P.S && !(live && P.cam.bounces != 0)) {
     B.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (P.full_shade) B.ctl[i] = 0u;
   }
@@ -286,8 +287,6 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     if (rng_dirty && P.rng_live) rng_store(B, i, rng);
     if (C.bounces != 0) {  // hitNearest: a ray with bounce == 0 hits nothing (draw.cu:294)
       has = true;
-      B.frames[(size_t)i] = make_float4(__uint_as_float(hdr_pack(T_W_PRIMARY, C.bounces, 0u)), 1.f, 1.f, 1.f);
-      if (P.full_shade) B.ctl[i] = 1u;
     } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
   }
   queue_append_block<8>(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, has, eye, dir, INFINITY, (unsigned)i, s_app);
@@ -349,7 +348,9 @@ __device__ __forceinline__ V3 rough_offset(float rough, Xorwow& rng, int zyx) {
 #ifndef RT_SHADE_MIN_CTAS
 #define RT_SHADE_MIN_CTAS 8
 #endif
-template <bool FULL>
+// FIRST = the iteration right after generate_kernel: every queue entry is a primary ray whose frame is the constant
+// (T_W_PRIMARY, bounces, weight 1) and whose accumulator is zero, so neither is stored by generate nor loaded here.
+template <bool FULL, bool FIRST>
 __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
                                                    const float4* __restrict__ qin, const unsigned n_front, const unsigned n_back,
                                                    float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
@@ -364,9 +365,9 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
     const float ht = hv.x; const int hid = __float_as_int(hv.y);
     const size_t S = (size_t)P.S;
     float4* const F = B.frames + i;  // frame slot (L,q) is F[(L*4+q)*S]
-    int sp = FULL ? (int)B.ctl[i] : 1;  // without mirrors, glass or GI exactly one frame is live while a ray is in flight
+    int sp = (FULL && !FIRST) ? (int)B.ctl[i] : 1;  // without mirrors, glass or GI exactly one frame is live while a ray is in flight
     Xorwow rng; bool rng_loaded = false, rng_dirty = false;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); bool acc_loaded = false, acc_dirty = false;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); bool acc_loaded = FIRST, acc_dirty = FIRST;  // FIRST: this visit writes the initial value
     bool overflow = false;
     const int nsuns = sc.num_suns, nlights = sc.num_suns + sc.num_bulbs;
     const float expose = P.cam.expose;
@@ -382,13 +383,13 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
 
     // ---- 1. resume the frame whose ray has just been traced ----
     sp--;
-    const float4 f0 = FR(sp, 0);
+    const float4 f0 = FIRST ? make_float4(__uint_as_float(hdr_pack(T_W_PRIMARY, P.cam.bounces, 0u)), 1.f, 1.f, 1.f) : FR(sp, 0);
     const unsigned hdr = __float_as_uint(f0.x);
     const unsigned type = hdr & 0xFFu;
     const int b = hdr_bounce(hdr);  // bounce of the traced ray
     const V3 Wt = mk3(f0.y, f0.z, f0.w);
 
-    if (type == T_DIFFUSE) {
+    if (!FIRST && type == T_DIFFUSE) {
       const float4 f1 = FR(sp, 1), f2 = FR(sp, 2), f3 = FR(sp, 3);
       li = (int)(hdr >> 8);
       df_point = mk3(f0.y, f0.z, f0.w); df_origin = mk3(f1.x, f1.y, f1.z); df_nrm = mk3(f1.w, f2.x, f2.y);
@@ -419,7 +420,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
         acc.x += df_w.x * er; acc.y += df_w.y * eg; acc.z += df_w.z * eb;
       }
       li++;
-    } else if (FULL && type == T_W_REFRACT1) {
+    } else if (FULL && !FIRST && type == T_W_REFRACT1) {
       // refractionLight after the inside ray, draw.cu:484-495 (a miss leaves the default ObjectInfo)
       V3 normal = mk3(0.f, 0.f, 0.f), ip = mk3(0.f, 0.f, 0.f); float ior = 1.458f;
       if (hid != -1) {
@@ -958,6 +959,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     RT_CUDA(cudaStreamSynchronize(st));
     unsigned n_front = rs->h_count[0], n_back = 0;  // primary rays all go to the front end
     float4 *qin = B.qa, *qout = B.qb;
+    int iter_in_pass = 0;
     while (n_front + n_back > 0) {
       iters++; rays += (uint64_t)n_front + n_back;
       RT_CUDA(cudaMemsetAsync(rs->counters, 0, 28, st));
@@ -966,8 +968,15 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
                                      rs->counters, rs->stats, B.fb_list);
       launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
       if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
-      if (P.full_shade) shade_kernel<true><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
-      else shade_kernel<false><<<(n_front + n_back + 127) / 128, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+      {
+        const unsigned sg = (n_front + n_back + 127) / 128;
+        const bool first = iter_in_pass == 0;
+        if (P.full_shade) { if (first) shade_kernel<true, true><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+                            else shade_kernel<true, false><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id); }
+        else { if (first) shade_kernel<false, true><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
+               else shade_kernel<false, false><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id); }
+        iter_in_pass++;
+      }
       launches++;
       RT_CUDA(cudaGetLastError());
       RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 20, cudaMemcpyDeviceToHost, st));
