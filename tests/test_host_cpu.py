@@ -199,3 +199,22 @@ def test_two_rank_partition_and_gather_gloo(tmp_path):
                         "--master-port", "29571", str(script), ROOT], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "ok0" in r.stdout and "ok1" in r.stdout
+
+
+def _run_cli(args, cwd):
+    import subprocess
+    exe = os.path.join(os.path.dirname(api.__file__), "raytracer")
+    assert os.path.exists(exe), "cuda_ray_tracer_b200/raytracer is not built"
+    return subprocess.run([exe] + args, capture_output=True, text=True, timeout=60, cwd=str(cwd))
+
+
+def test_cli_error_paths(tmp_path):
+    """parse.cpp:22-25 / 218-221: a missing file and an invalid line end the program with exit code 1 and the reference's text."""
+    r = _run_cli([str(tmp_path / "nope.txt")], tmp_path)
+    assert r.returncode == 1 and "Error opening file" in r.stdout
+    bad = tmp_path / "bad.txt"
+    bad.write_text("png 8 8 x.png\nsphere 0 0\n")
+    r = _run_cli([str(bad)], tmp_path)
+    assert r.returncode == 1 and "One of the lines are not valid" in r.stdout
+    r = _run_cli([], tmp_path)
+    assert r.returncode == 1 and "usage" in r.stderr

@@ -349,3 +349,35 @@ def test_exact_lane_equals_reference_order_sphere_field():
         assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"])
     a2 = sc.render(240, 135, 16, api.SPP_TRUE | api.TRAVERSE_REF_ORDER); a3 = sc.render(240, 135, 16, api.SPP_TRUE)
     assert np.array_equal(a2["rgba"], a3["rgba"]) and a2["counters"].rays == a3["counters"].rays
+
+
+# ---- the drop-in command line: `raytracer <scene.txt>` (main.cu:25-94) ----
+def _run_cli(args, cwd):
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(api.__file__), "raytracer")
+    assert os.path.exists(exe), "cuda_ray_tracer_b200/raytracer is not built (python -c 'import __graft_entry__ as g; g.build()')"
+    return subprocess.run([exe] + args, capture_output=True, text=True, timeout=600, cwd=str(cwd))
+
+
+@pytest.mark.parametrize("bounds", ["computed", "shipped"])
+def test_cli_writes_the_same_png_as_the_api(bounds, tmp_path):
+    """The CLI parses the scene text itself, prints the reference's stdout lines, and writes the PNG named on the
+    scene's `png` line into the CWD; its bytes must equal Scene.render through the ctypes binding."""
+    cfg, a = synth.soup(5000, seed=11, width=160, height=90, aa=4)
+    path = str(tmp_path / "scene.txt")
+    synth.write_scene_text(path, cfg, a, name="cli_out.png")
+    ids_path = str(tmp_path / "ids.bin")
+    r = _run_cli([path, "--bounds", bounds, "--counters", "--ids", ids_path], tmp_path)
+    assert r.returncode == 0, r.stderr
+    for line in ("Initialize raw config time:", "LBVH Build time (N=5000):", "Render time:", "Transfer to host time:", "cudaFree time:"):
+        assert line in r.stdout, (line, r.stdout)
+    img = api.png_read(str(tmp_path / "cli_out.png"))
+    hs = api.parse_scene_file(path)
+    sc = api.Scene(hs.desc, keepalive=hs)
+    sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED if bounds == "computed" else api.BOUNDS_FROM_DESC)
+    out = sc.render(want_ids=True)
+    assert img.shape == (90, 160, 4)
+    assert np.array_equal(img, out["rgba"])
+    assert np.array_equal(np.fromfile(ids_path, np.int32).reshape(90, 160), out["ids"])
+
