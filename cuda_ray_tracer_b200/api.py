@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libb200rt.so")  # RT_LIB: experiment builds (Makefile LIB=...)
 
 BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN = 0, 1, 2
-SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE, TRAVERSE_REF_ORDER = 0, 1, 2, 4, 8, 16, 32
+SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE, TRAVERSE_REF_ORDER, RENDER_OVERLAP_BUILD = 0, 1, 2, 4, 8, 16, 32, 64
 
 
 class RtError(RuntimeError):
@@ -58,7 +58,7 @@ class Counters(C.Structure):
 
 _lib = None
 
-EXPORTS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_update_triangles", "rt_build_lbvh", "rt_render", "rt_render_host",
+EXPORTS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_update_triangles", "rt_build_lbvh", "rt_scene_build_ms", "rt_scene_begin_frame", "rt_render", "rt_render_host",
            "rt_trace", "rt_export_reference_layout", "rt_scene_num_prims", "rt_parse_scene_file", "rt_host_scene_desc",
            "rt_host_scene_filename", "rt_host_scene_bounds", "rt_host_scene_free", "rt_triangle_setup", "rt_png_write",
            "rt_png_read", "rt_free", "rt_xorwow_init", "rt_last_error", "rt_version"]
@@ -80,6 +80,8 @@ def load_library():
     L.rt_scene_destroy.argtypes = [vp]
     L.rt_scene_update_triangles.argtypes = [vp, vp, vp, vp, vp]
     L.rt_build_lbvh.argtypes = [vp, ip, C.c_uint, vp, C.POINTER(C.c_float)]
+    L.rt_scene_begin_frame.argtypes = [vp, vp]
+    L.rt_scene_build_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.rt_render.argtypes = [vp, ip, ip, ip, C.c_uint, C.POINTER(TileSet), vp, vp, vp, C.POINTER(Counters), vp]
     L.rt_render_host.argtypes = [vp, ip, ip, ip, C.c_uint, C.POINTER(TileSet), vp, vp, vp, C.POINTER(Counters)]
     L.rt_trace.argtypes = [vp, ip, vp, vp, C.c_uint, vp, vp, C.POINTER(Counters), vp]
@@ -215,6 +217,16 @@ class Scene:
         ms = C.c_float(0)
         _check(load_library().rt_build_lbvh(self.h, morton_bits, flags, stream, C.byref(ms) if timed else None), "rt_build_lbvh")
         return ms.value
+
+    def build_ms(self):
+        """device time of the last build, read after the fact (keeps a frame loop asynchronous)"""
+        ms = C.c_float(0)
+        _check(load_library().rt_scene_build_ms(self.h, C.byref(ms)), "rt_scene_build_ms")
+        return ms.value
+
+    def begin_frame(self, stream=None):
+        """fork point of RENDER_OVERLAP_BUILD, when the frame starts before update_triangles (e.g. with an upload)"""
+        _check(load_library().rt_scene_begin_frame(self.h, stream), "rt_scene_begin_frame")
 
     def update_triangles(self, p0, p1, p2, stream=None):
         keep = [a if hasattr(a, "data_ptr") else _f32(a) for a in (p0, p1, p2)]

@@ -247,8 +247,10 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
   RT_CUDA(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
   uint32_t launches = 0;
-  if (ms_out) RT_CUDA(cudaEventRecord(s->ev0, st));
-  int rc = rt_build_codes_and_sort(s, morton_bits, flags, st, &launches);
+  int rc = rt_arm_fork(s, st);
+  if (rc) return rc;
+  RT_CUDA(cudaEventRecord(s->ev0, st));
+  rc = rt_build_codes_and_sort(s, morton_bits, flags, st, &launches);
   if (rc) return rc;
   const int n = s->n, grid = (n + 255) / 256;
   int* root_dev = (int*)(s->bounds + 8);
@@ -267,12 +269,20 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
   }
   RT_CUDA(cudaGetLastError());
   s->built = true; s->built_bits = morton_bits; s->built_topdown = (flags & RT_BUILD_TOPDOWN) != 0;
-  s->root = INT32_MIN;  // fetched lazily (rt_scene_root) so that the build stays asynchronous
+  RT_CUDA(cudaEventRecord(s->ev1, st));
   if (ms_out) {
-    RT_CUDA(cudaEventRecord(s->ev1, st));
     RT_CUDA(cudaEventSynchronize(s->ev1));
     RT_CUDA(cudaEventElapsedTime(ms_out, s->ev0, s->ev1));
   }
+  return RT_OK;
+}
+
+extern "C" int rt_scene_build_ms(rt_scene* s, float* ms_out) {
+  if (!s || !ms_out) { rt_set_error("rt_scene_build_ms: null argument"); return RT_ERR_INVALID; }
+  if (!s->built) { rt_set_error("rt_scene_build_ms: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
+  RT_CUDA(cudaSetDevice(s->device));
+  RT_CUDA(cudaEventSynchronize(s->ev1));
+  RT_CUDA(cudaEventElapsedTime(ms_out, s->ev0, s->ev1));
   return RT_OK;
 }
 
@@ -281,6 +291,7 @@ extern "C" int rt_export_reference_layout(rt_scene* s, uint32_t* codes, uint64_t
   if (!s->built) { rt_set_error("rt_export_reference_layout: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
   RT_CUDA(cudaSetDevice(s->device));
   RT_CUDA(cudaDeviceSynchronize());
+  s->fork_armed = false;
   const int n = s->n;
   if (codes) {
     if (!s->sorted_keys32) { rt_set_error("rt_export_reference_layout: built with 63-bit codes, pass codes64"); return RT_ERR_INVALID; }

@@ -58,7 +58,7 @@ struct RtCamera {
 
 struct RtDeviceScene {  // device pointers, passed to kernels by value
   int n;                // primitives
-  int root;             // root node slot (or leaf ref if n == 1)
+  const int* root;      // device word holding the root node slot (or leaf ref if n == 1): read by the kernels, never by the host
   const float4* nodes;
   const float4* sorted_tv;
   const uint32_t* perm;  // sorted position -> file-order index
@@ -90,12 +90,14 @@ struct rt_scene {
   int* node_karras = nullptr;      // [n-1] slot -> reference (Karras) internal index
   float* bounds = nullptr;         // 6 floats (min3,max3) as ordered ints during reduction
   uint32_t* sorted_keys32 = nullptr; uint64_t* sorted_keys64 = nullptr; uint32_t* sorted_perm = nullptr;
-  int root = 0;
   bool built = false; int built_bits = 0; bool built_topdown = false;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the last build (rt_scene_build_ms)
+  // RT_RENDER_OVERLAP_BUILD: the point in the caller's stream before this frame's update/build work
+  cudaEvent_t ev_fork = nullptr; cudaStream_t fork_stream = nullptr; bool fork_armed = false;
   float* upd_stage[3] = {nullptr, nullptr, nullptr};  // device staging of host vertex arrays (rt_scene_update_triangles)
   // render state (allocated lazily, reused)
   void* rstate = nullptr;
 };
 
 int rt_render_free_state(rt_scene* s);
+int rt_arm_fork(rt_scene* s, cudaStream_t st);

@@ -716,6 +716,7 @@ struct RenderState {
   uint32_t* h_count = nullptr;  // pinned
   RngTables rng;
   cudaEvent_t e0 = nullptr, e1 = nullptr, t0 = nullptr, t1 = nullptr;
+  cudaStream_t head_stream = nullptr; cudaEvent_t ev_join = nullptr;  // RT_RENDER_OVERLAP_BUILD
   int trav_grid = 0;
   uint8_t* d_rgba = nullptr; int32_t* d_ids = nullptr; uint8_t* d_written = nullptr; size_t img_px = 0;  // rt_render_host staging
   float4* trace_q = nullptr; float2* trace_hits = nullptr; unsigned* trace_fb = nullptr; size_t trace_cap = 0;
@@ -743,17 +744,9 @@ int ensure_common(rt_scene* s, RenderState* st) {
   return RT_OK;
 }
 
-int fetch_root(rt_scene* s) {
-  if (s->n > 0 && s->root == INT32_MIN) {
-    RT_CUDA(cudaDeviceSynchronize());
-    RT_CUDA(cudaMemcpy(&s->root, s->bounds + 8, 4, cudaMemcpyDeviceToHost));
-  }
-  return RT_OK;
-}
-
 RtDeviceScene device_scene(const rt_scene* s) {
   RtDeviceScene d;
-  d.n = s->n; d.root = s->n > 0 ? s->root : 0; d.nodes = s->nodes; d.sorted_tv = s->sorted_tv; d.perm = s->sorted_perm; d.prim_mat = s->prim_mat;
+  d.n = s->n; d.root = (const int*)(s->bounds + 8); d.nodes = s->nodes; d.sorted_tv = s->sorted_tv; d.perm = s->sorted_perm; d.prim_mat = s->prim_mat;
   d.suns = s->suns; d.num_suns = s->cfg.num_suns; d.bulbs = s->bulbs; d.num_bulbs = s->cfg.num_bulbs;
   d.planes = s->planes; d.num_planes = s->cfg.num_planes;
   return d;
@@ -840,6 +833,7 @@ int rt_render_free_state(rt_scene* s) {
   cudaFree(st->rng.mats); cudaFree(st->rng.nib); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
   cudaFree(st->trace_q); cudaFree(st->trace_hits); cudaFree(st->trace_fb);
   if (st->e0) { cudaEventDestroy(st->e0); cudaEventDestroy(st->e1); cudaEventDestroy(st->t0); cudaEventDestroy(st->t1); }
+  if (st->head_stream) { cudaStreamDestroy(st->head_stream); cudaEventDestroy(st->ev_join); }
   delete st;
   s->rstate = nullptr;
   return RT_OK;
@@ -857,7 +851,6 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   cudaStream_t st = (cudaStream_t)stream;
   RenderState* rs = get_state(s);
   int rc = ensure_common(s, rs); if (rc) return rc;
-  rc = fetch_root(s); if (rc) return rc;
 
   RenderParams P; memset(&P, 0, sizeof(P));
   RtCamera& C = P.cam;
@@ -935,26 +928,45 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
   const RtDeviceScene sc = device_scene(s);
 
+  // The head of the frame (clears, RNG seeding and primary ray generation of the first pass) reads nothing the build
+  // writes.  With RT_RENDER_OVERLAP_BUILD it runs on its own stream from the point in `st` before this frame's
+  // update/build calls (s->ev_fork) and joins `st` before the first traversal.
+  const bool overlap = (flags & RT_RENDER_OVERLAP_BUILD) && s->fork_armed && s->fork_stream == st && !getenv("RT_NO_OVERLAP");
+  s->fork_armed = false;
+  cudaStream_t hs = st;
+  if (overlap) {
+    if (!rs->head_stream) {
+      RT_CUDA(cudaStreamCreateWithFlags(&rs->head_stream, cudaStreamNonBlocking));
+      RT_CUDA(cudaEventCreateWithFlags(&rs->ev_join, cudaEventDisableTiming));
+    }
+    hs = rs->head_stream;
+    RT_CUDA(cudaStreamWaitEvent(hs, s->ev_fork, 0));
+  }
   RT_CUDA(cudaEventRecord(rs->e0, st));
-  RT_CUDA(cudaMemsetAsync(d_rgba, 0, (size_t)npx * 4, st));
-  if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, st));
-  if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, st));
-  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
-  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, st));
+  RT_CUDA(cudaMemsetAsync(d_rgba, 0, (size_t)npx * 4, hs));
+  if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, hs));
+  if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, hs));
+  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, hs));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, hs));
   uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0; uint32_t trav_launches = 0;
   for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
     P.slot0 = (int)slot0; P.npix = (int)std::min<long long>(npix_pass, nslots - slot0); P.S = P.npix * P.spp;
     passes++;
     samples += (uint64_t)P.S;
-    RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, st));
+    RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, hs));
     if (P.mode != 2 && P.need_rng) {
       const int hn = (int)(((npx + 255) / 256 + 31) & ~31ll);
-      rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, st>>>(P, B, hn);
+      rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, hs>>>(P, B, hn);
       launches++;
     }
-    generate_kernel<<<(unsigned)((P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, st>>>(P, B, B.qa, d_hit_id);
+    generate_kernel<<<(unsigned)((P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, hs>>>(P, B, B.qa, d_hit_id);
     launches++;
     RT_CUDA(cudaGetLastError());
+    if (hs != st) {  // join: everything below is ordered after both the build and the head
+      RT_CUDA(cudaEventRecord(rs->ev_join, hs));
+      RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join, 0));
+      hs = st;
+    }
     RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 4, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));
     unsigned n_front = rs->h_count[0], n_back = 0;  // primary rays all go to the front end
@@ -990,6 +1002,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     resolve_kernel<<<(P.npix + 127) / 128, 128, 0, st>>>(P, B, d_rgba, d_written);
     launches++;
     RT_CUDA(cudaGetLastError());
+  }
+  if (hs != st) {  // nothing to render: the clears still belong to this call
+    RT_CUDA(cudaEventRecord(rs->ev_join, hs));
+    RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join, 0));
   }
   RT_CUDA(cudaEventRecord(rs->e1, st));
   RT_CUDA(cudaEventSynchronize(rs->e1));
@@ -1034,9 +1050,9 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   if (s->n > 0 && !s->built) { rt_set_error("rt_trace: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
   RT_CUDA(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
+  s->fork_armed = false;
   RenderState* rs = get_state(s);
   int rc = ensure_common(s, rs); if (rc) return rc;
-  rc = fetch_root(s); if (rc) return rc;
   if (n == 0) return RT_OK;
   if ((size_t)n > rs->trace_cap) {
     cudaFree(rs->trace_q); cudaFree(rs->trace_hits); cudaFree(rs->trace_fb); rs->trace_q = nullptr; rs->trace_hits = nullptr; rs->trace_fb = nullptr; rs->trace_cap = 0;

@@ -208,7 +208,8 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
     if ((e = cudaMemcpy(&f, flagbuf.p, 4, cudaMemcpyDeviceToHost))) return fail(e, "flags readback");
     s->any_shiny = f & 1; s->any_trans = f & 2; s->any_rough = f & 4;
   }
-  if ((e = cudaEventCreate(&s->ev0)) || (e = cudaEventCreate(&s->ev1))) return fail(e, "events");
+  if ((e = cudaEventCreate(&s->ev0)) || (e = cudaEventCreate(&s->ev1)) || (e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)))
+    return fail(e, "events");
   *out = s;
   return RT_OK;
 }
@@ -219,10 +220,27 @@ extern "C" int rt_scene_destroy(rt_scene* s) {
   rt_render_free_state(s);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->ev_fork) cudaEventDestroy(s->ev_fork);
   for (int k = 0; k < 3; k++) cudaFree(s->upd_stage[k]);
   cudaFree(s->arena);
   delete s;
   return RT_OK;
+}
+
+// RT_RENDER_OVERLAP_BUILD: remember the point in `st` before this frame's first update/build call.  rt_render may start the
+// BVH-independent head of the frame (image clear, primary ray generation) from there on a side stream.
+int rt_arm_fork(rt_scene* s, cudaStream_t st) {
+  if (s->fork_armed && s->fork_stream == st) return RT_OK;
+  RT_CUDA(cudaEventRecord(s->ev_fork, st));
+  s->fork_stream = st; s->fork_armed = true;
+  return RT_OK;
+}
+
+extern "C" int rt_scene_begin_frame(rt_scene* s, void* stream) {
+  if (!s) { rt_set_error("rt_scene_begin_frame: null scene"); return RT_ERR_INVALID; }
+  RT_CUDA(cudaSetDevice(s->device));
+  s->fork_armed = false;
+  return rt_arm_fork(s, (cudaStream_t)stream);
 }
 
 extern "C" int rt_scene_update_triangles(rt_scene* s, const float* p0, const float* p1, const float* p2, void* stream) {
@@ -230,6 +248,7 @@ extern "C" int rt_scene_update_triangles(rt_scene* s, const float* p0, const flo
   if (s->nt == 0) return RT_OK;
   RT_CUDA(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
+  rt_arm_fork(s, st);
   const float* src[3] = {p0, p1, p2};
   const float* dev[3];
   bool staged = false;

@@ -206,7 +206,7 @@ __device__ __forceinline__ RtHit rt_trace_ref(const RtDeviceScene& sc, const V3 
     const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
     unsigned loc_ref[RT_STACK_TOTAL - RT_STACK_SHARED];
     int sp = 0;
-    unsigned cur = (unsigned)sc.root;
+    unsigned cur = (unsigned)__ldg(sc.root);
     const int tid = threadIdx.x;
     while (true) {
       bool pop = false;
@@ -417,7 +417,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
             const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
             omk = (4e-7f * 1.000001f) * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
             q2 = rt_ray2(o, inv);
-            tmax = tlimit; tcull = tlimit; tcut = tlimit * 1.000001f; t2 = INFINITY; best = -1; sp = 0; cur = (unsigned)sc.root;
+            tmax = tlimit; tcull = tlimit; tcut = tlimit * 1.000001f; t2 = INFINITY; best = -1; sp = 0; cur = sc.n > 0 ? (unsigned)__ldg(sc.root) : 0u;
             // a sun ray never culls by distance (tcull stays +INF) and needs no certificate
             fl = (anyhit ? F_ANYHIT : 0u) | ((!SUN && !(anyhit && tlimit == INFINITY)) ? F_WANTKEY : 0u);
             st = sc.n > 0 ? ACTIVE : DONE;  // n == 0: planes only.  n == 1: the root is the leaf

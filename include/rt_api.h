@@ -77,6 +77,9 @@ enum {
                                   separate refit instead of the fused bottom-up builder           */
 };
 int rt_build_lbvh(rt_scene* scene, int morton_bits, unsigned flags, void* stream, float* ms_out);
+/* Device time of the last rt_build_lbvh (the number lbvh_builder.cu:489 prints), read AFTER the fact so
+ * that a frame loop can keep the build asynchronous (ms_out = NULL): waits for that build only. */
+int rt_scene_build_ms(rt_scene* scene, float* ms_out);
 
 /* ---- render ----------------------------------------------------------------------------------
  * replaces render(pixel_t* d_image, int w, int h, int aa, RawConfig* d_cfg) (include/draw.cuh:10,
@@ -102,9 +105,18 @@ enum {
                                  (draw.cu:335-337): z,y,x instead of x,y,z                          */
   RT_COUNTERS         = 8u,   /* fill node/leaf counters (slower kernels) and traverse_ms          */
   RT_TIME_TRAVERSE    = 16u,  /* fill traverse_ms (CUDA events around the traverse launches) only  */
-  RT_TRAVERSE_REF_ORDER = 32u /* every ray in the reference's left-first visiting order
+  RT_TRAVERSE_REF_ORDER = 32u, /* every ray in the reference's left-first visiting order
                                  (bvh_traversal.cu:149-179): the exact lane's fallback, for all rays */
+  RT_RENDER_OVERLAP_BUILD = 64u /* frame loops (update -> build -> render on ONE stream): run the part of the
+                                 frame that does not read the BVH (image clear, primary ray generation of the
+                                 first pass) on an internal stream that forks from `stream` at the frame's
+                                 first rt_scene_update_triangles / rt_build_lbvh call, i.e. concurrently with
+                                 the build.  The caller promises that nothing it enqueued on `stream` after
+                                 that call touches the render's output buffers.  Same pixels either way.
+                                 rt_scene_begin_frame moves the fork point earlier (e.g. before the caller's
+                                 own vertex upload)                                                        */
 };
+int rt_scene_begin_frame(rt_scene* scene, void* stream);
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
   int32_t tile_w, tile_h, num_ranks, rank;
 } rt_tile_set;

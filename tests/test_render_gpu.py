@@ -381,3 +381,33 @@ def test_cli_writes_the_same_png_as_the_api(bounds, tmp_path):
     assert np.array_equal(img, out["rgba"])
     assert np.array_equal(np.fromfile(ids_path, np.int32).reshape(90, 160), out["ids"])
 
+
+def test_frame_loop_overlapped_head_gives_the_same_pixels():
+    """RT_RENDER_OVERLAP_BUILD: clears + primary ray generation run beside the (asynchronous) build of the same frame.
+    Three frames of update -> build -> render on one stream, with and without the flag: identical bytes and ids."""
+    import torch
+    cfg, a = synth.soup(60000, seed=5, width=640, height=360, aa=4)
+    a = synth.finish_triangles(a)
+    desc, keep = api.make_desc(cfg, a)
+    sc = api.Scene(desc, 0)
+    p0, p1, p2 = (np.ascontiguousarray(x, np.float32) for x in a["tri"][:3])
+    out = {}
+    for flag in (0, api.RENDER_OVERLAP_BUILD):
+        for f in range(3):
+            shift = np.float32(0.01 * f)
+            d = [torch.from_numpy(x + shift).cuda() for x in (p0, p1, p2)]
+            img = torch.full((360, 640, 4), 7, dtype=torch.uint8, device="cuda")
+            ids = torch.full((360, 640), 5, dtype=torch.int32, device="cuda")
+            if flag and f == 1:
+                sc.begin_frame()  # explicit fork point, before the update
+            sc.update_triangles(d[0], d[1], d[2])
+            sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED, timed=False)
+            cnt = api.Counters()
+            sc.render_device(640, 360, 4, img, flags=api.SPP_TRUE | flag, d_ids=ids, counters=cnt)
+            torch.cuda.synchronize()
+            assert sc.build_ms() > 0.0
+            out[(flag, f)] = (img.cpu().numpy(), ids.cpu().numpy(), cnt.rays)
+    for f in range(3):
+        a0, a1 = out[(0, f)], out[(api.RENDER_OVERLAP_BUILD, f)]
+        assert np.array_equal(a0[0], a1[0]) and np.array_equal(a0[1], a1[1]) and a0[2] == a1[2]
+    assert not np.array_equal(out[(0, 0)][0], out[(0, 2)][0])  # the frames do differ
