@@ -218,3 +218,136 @@ def test_cli_error_paths(tmp_path):
     assert r.returncode == 1 and "One of the lines are not valid" in r.stdout
     r = _run_cli([], tmp_path)
     assert r.returncode == 1 and "usage" in r.stderr
+
+
+# ---- chunk-parallel parser --------------------------------------------------------------
+HOST_ARRAYS = [("sphere_c", "num_spheres", 3), ("sphere_r", "num_spheres", 1), ("sphere_mat", "num_spheres", 11), ("tri_p0", "num_triangles", 3),
+               ("tri_p1", "num_triangles", 3), ("tri_p2", "num_triangles", 3), ("tri_nor", "num_triangles", 3), ("tri_e1", "num_triangles", 3),
+               ("tri_e2", "num_triangles", 3), ("tri_mat", "num_triangles", 11), ("suns", "num_suns", 6), ("bulbs", "num_bulbs", 6),
+               ("planes", "num_planes", 21)]
+
+
+def _parse_with(path, threads, chunk_bytes, monkeypatch):
+    monkeypatch.setenv("RT_PARSE_THREADS", str(threads))
+    monkeypatch.setenv("RT_PARSE_CHUNK_BYTES", str(chunk_bytes))
+    return api.parse_scene_file(path)
+
+
+def _same_host_scene(a, b):
+    da, db = a.desc, b.desc
+    assert bytes(da)[:C.sizeof(api.SceneDesc)] != b"" and a.filename == b.filename
+    for f in ("width", "height", "bounces", "aa", "gi", "fisheye", "panorama", "num_spheres", "num_triangles", "num_prims", "num_suns",
+              "num_bulbs", "num_planes"):
+        assert getattr(da, f) == getattr(db, f), f
+    for f in ("color", "shine", "trans", "forward", "right", "up", "eye", "target_up"):
+        assert np.array_equal(np.array(getattr(da, f)[:], np.float32).view(np.uint32), np.array(getattr(db, f)[:], np.float32).view(np.uint32)), f
+    for f in ("dof_focus", "dof_lens", "expose", "ior", "rough"):
+        assert np.array_equal(np.float32(getattr(da, f)).view(np.uint32), np.float32(getattr(db, f)).view(np.uint32)), f
+    for name, cnt, w in HOST_ARRAYS:
+        n = getattr(da, cnt)
+        assert np.array_equal(a.array(name, (n, w)).view(np.uint32), b.array(name, (n, w)).view(np.uint32)), name
+    assert np.array_equal(a.array("refs", (da.num_prims, 2), np.int32), b.array("refs", (da.num_prims, 2), np.int32))
+    for x, y in zip(a.bounds(), b.bounds()):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
+
+
+def _stateful_scene_text(n, seed):
+    """Every kind of line, material changes between primitives, absolute and relative vertex indices that reach far
+    back (across chunk borders), camera lines in the middle of the file."""
+    rng = np.random.RandomState(seed)
+    out = ["png 64 48 stateful.png", "eye 0 0 3", "bounces 3"]
+    nv = 0
+    for i in range(n):
+        r = rng.randint(0, 100)
+        if r < 45 or nv < 3:
+            out.append("xyz %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 3).astype(np.float32))); nv += 1
+        elif r < 70:
+            if rng.randint(2):
+                idx = rng.randint(1, nv + 1, 3)          # absolute, 1-based, anywhere in the file so far
+            else:
+                idx = -rng.randint(1, min(nv, 400) + 1, 3)  # relative to the current end of the list
+            out.append("tri %d %d %d" % tuple(idx))
+        elif r < 78:
+            out.append("sphere %.9g %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 4).astype(np.float32)))
+        elif r < 84:
+            out.append("color %.9g %.9g %.9g" % tuple(rng.uniform(0, 1, 3).astype(np.float32)))
+        elif r < 87:
+            out.append("shininess %.9g" % rng.uniform(0, 1) if rng.randint(2) else "shininess %.9g %.9g %.9g" % tuple(rng.uniform(0, 1, 3)))
+        elif r < 90:
+            out.append("transparency %.9g" % rng.uniform(0, 1) if rng.randint(2) else "transparency %.9g %.9g %.9g" % tuple(rng.uniform(0, 1, 3)))
+        elif r < 92:
+            out.append("ior %.9g" % rng.uniform(1, 2))
+        elif r < 94:
+            out.append("roughness %.9g" % rng.uniform(0, 0.3))
+        elif r < 95:
+            out.append("sun %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 3)))
+        elif r < 96:
+            out.append("bulb %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 3)))
+        elif r < 97:
+            out.append("plane %.9g %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 4)))
+        elif r < 98:
+            out.append(["forward %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 3)), "up %.9g %.9g %.9g" % tuple(rng.uniform(-1, 1, 3)),
+                        "expose %.9g" % rng.uniform(1, 3), "aa %d" % rng.randint(1, 40), "dof 2.5 0.01", "gi 2"][rng.randint(6)])
+        else:
+            out.append(["", "   \t ", " "][rng.randint(3)])
+    return "\n".join(out) + "\n"
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_parser_chunked_equals_serial(seed, tmp_path, monkeypatch):
+    p = tmp_path / "stateful.txt"
+    p.write_text(_stateful_scene_text(6000, seed))
+    serial = _parse_with(str(p), 1, 1 << 40, monkeypatch)
+    assert serial.desc.num_triangles > 500 and serial.desc.num_spheres > 100 and serial.desc.num_planes > 10
+    for threads, chunk in ((4, 4096), (3, 700), (8, 64)):
+        _same_host_scene(serial, _parse_with(str(p), threads, chunk, monkeypatch))
+    # and against the reference's own parseInput (oracle/_ref/libref_host.so = src/parse.cpp compiled for the host)
+    import ref_lib
+    if ref_lib.available():
+        r = ref_lib.RefScene(str(p)); ra = r.arrays(); d = serial.desc
+        assert (d.num_spheres, d.num_triangles, d.num_prims, d.num_suns, d.num_bulbs, d.num_planes) == tuple(
+            r.n[k] for k in ("spheres", "triangles", "prims", "suns", "bulbs", "planes"))
+        eq = lambda x, y: np.array_equal(np.ascontiguousarray(x).view(np.uint32), np.ascontiguousarray(y).view(np.uint32))
+        for name, cnt, w in HOST_ARRAYS:
+            if name.startswith("tri_") and name != "tri_mat":
+                continue
+            assert eq(serial.array(name, (getattr(d, cnt), w)).reshape(ra[name].shape), ra[name]), name
+        for k, f in enumerate(("tri_p0", "tri_p1", "tri_p2", "tri_nor", "tri_e1", "tri_e2")):
+            assert eq(serial.array(f, (d.num_triangles, 3)), ra["tri"][k]), f
+        assert np.array_equal(serial.array("refs", (d.num_prims, 2), np.int32), ra["refs"])
+
+
+@pytest.mark.skipif(not have_scenes, reason="scene fixtures not present")
+@pytest.mark.parametrize("name", ["redchair", "tenthousand", "spiral"])
+def test_parser_chunked_equals_serial_on_reference_scenes(name, tmp_path, monkeypatch):
+    path = os.path.join(O.SCENE_DIR, name + ".txt")
+    _same_host_scene(_parse_with(path, 1, 1 << 40, monkeypatch), _parse_with(path, 4, 2048, monkeypatch))
+
+
+def test_parser_chunked_reports_the_first_bad_line(tmp_path, monkeypatch):
+    lines = _stateful_scene_text(3000, 7).split("\n")[:-1]
+    n = len(lines)
+    cases = {"unknown keyword": (n // 3, "frobnicate 1 2"), "bad float in a primitive": (n // 2, "sphere 0 0 zero 1"),
+             "bad vertex": (n // 5, "xyz 1 2 three"), "index out of range": (n // 4, "tri 1 2 999999"), "bad camera line": (n // 6, "aa many"),
+             "bad material": (n // 7, "color 1 x 1")}
+    for what, (at, text) in cases.items():
+        bad = list(lines); bad[at] = text
+        bad[at + 40] = "another bad line"  # a later error must not win
+        p = tmp_path / "bad.txt"; p.write_text("\n".join(bad) + "\n")
+        for threads, chunk in ((1, 1 << 40), (4, 1024), (8, 64)):
+            with pytest.raises(api.RtError, match=r"One of the lines are not valid. \(.*:%d\)" % (at + 1)):
+                _parse_with(str(p), threads, chunk, monkeypatch)
+
+
+def test_parser_number_syntax_follows_stof(tmp_path):
+    """std::stof / std::stoi (parse.cpp:47-215) take strtof/strtol syntax: leading '+', hex floats, inf/nan, trailing junk after a valid prefix."""
+    p = tmp_path / "n.txt"
+    p.write_text("png +8 0x8 n.png\neye +1.5 0x1p-1 -.5e1\nexpose 2.5abc\nior inf\nroughness 1e-50\nsphere 1. .5 -0 1e0\n")
+    hs = api.parse_scene_file(str(p)); d = hs.desc
+    assert (d.width, d.height) == (8, 0)  # stoi("0x8") stops after the 0, base 10
+    assert tuple(d.eye[:]) == (1.5, 0.5, -5.0) and d.expose == 2.5 and np.isinf(d.ior) and d.rough == 0.0
+    assert np.array_equal(hs.array("sphere_c", (1, 3)), np.array([[1.0, 0.5, -0.0]], np.float32)) and np.signbit(hs.array("sphere_c", (1, 3))[0, 2])
+    for bad in ("eye +-1 0 0\n", "eye . 0 0\n", "eye e5 0 0\n", "aa +\n"):
+        p.write_text(bad)
+        with pytest.raises(api.RtError):
+            api.parse_scene_file(str(p))
