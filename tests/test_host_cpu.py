@@ -351,3 +351,49 @@ def test_parser_number_syntax_follows_stof(tmp_path):
         p.write_text(bad)
         with pytest.raises(api.RtError):
             api.parse_scene_file(str(p))
+
+
+# ---- row-block-parallel PNG encoder ------------------------------------------------------
+def _decode_png_independently(path):
+    """Minimal PNG reader on Python's zlib (checks every chunk CRC and, through zlib.decompress, the Adler-32 of the
+    stitched stream); only filter types 0/1, which is what the writer emits."""
+    import struct
+    import zlib
+    b = open(path, "rb").read()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n"
+    pos = 8; idat = b""; ihdr = None; kinds = []
+    while pos < len(b):
+        (n,) = struct.unpack(">I", b[pos:pos + 4]); typ = b[pos + 4:pos + 8]; data = b[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", b[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(typ + data) == crc, typ
+        kinds.append(typ)
+        if typ == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", data)
+        elif typ == b"IDAT":
+            idat += data
+        pos += 12 + n
+    assert kinds[0] == b"IHDR" and kinds[-1] == b"IEND" and pos == len(b)
+    w, h, depth, ctype, comp, filt, inter = ihdr
+    assert (depth, ctype, comp, filt, inter) == (8, 6, 0, 0, 0)
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, w * 4 + 1)
+    assert set(np.unique(raw[:, 0])) <= {0, 1}
+    px = raw[:, 1:].reshape(h, w, 4)
+    out = np.cumsum(px.astype(np.uint32), axis=1).astype(np.uint8)  # Sub filter: running sum over the pixels of a row, mod 256
+    return np.where((raw[:, 0] == 1)[:, None, None], out, px)
+
+
+@pytest.mark.parametrize("shape,threads", [((1, 1), 4), ((7, 3), 8), ((300, 257), 1), ((1100, 640), 3), ((2160, 1024), 8)])
+def test_png_parallel_encoder_is_a_valid_png(shape, threads, tmp_path, monkeypatch):
+    h, w = shape
+    rng = np.random.RandomState(h * 131 + w)
+    img = rng.randint(0, 256, (h, w, 4)).astype(np.uint8)
+    img[h // 3:, : w // 2] = (10, 200, 30, 255)  # flat areas and noise
+    monkeypatch.setenv("RT_PNG_THREADS", str(threads))
+    p = str(tmp_path / "p.png")
+    api.png_write(p, img)
+    assert np.array_equal(_decode_png_independently(p), img)
+    assert np.array_equal(api.png_read(p), img)
+    monkeypatch.setenv("RT_PNG_THREADS", "1")
+    q = str(tmp_path / "q.png")
+    api.png_write(q, img)
+    assert np.array_equal(_decode_png_independently(q), img)
