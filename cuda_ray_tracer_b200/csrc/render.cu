@@ -730,7 +730,7 @@ RenderState* get_state(rt_scene* s) {
 int ensure_common(rt_scene* s, RenderState* st) {
   if (!st->counters) {
     RT_CUDA(cudaMalloc(&st->counters, 64));
-    RT_CUDA(cudaMalloc(&st->stats, 64));
+    RT_CUDA(cudaMalloc(&st->stats, 128));
     RT_CUDA(cudaMallocHost(&st->h_count, 64));
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
     RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
@@ -946,7 +946,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   RT_CUDA(cudaMemsetAsync(d_rgba, 0, (size_t)npx * 4, hs));
   if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, hs));
   if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, hs));
-  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, hs));
+  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 128, hs));
   RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, hs));
   uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0; uint32_t trav_launches = 0;
   for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
@@ -1018,6 +1018,13 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     unsigned long long hs[3];
     RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
     counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1]; counters->shaded_hits = hs[2];
+#ifdef RT_LANE_STATS
+    if (count) {
+      unsigned long long q[9]; RT_CUDA(cudaMemcpy(q, rs->stats, 72, cudaMemcpyDeviceToHost));
+      fprintf(stderr, "[lane stats] node-phase iters %llu avg lanes %.2f (parked at leaf %.2f) | leaf-phase iters %llu avg lanes %.2f | idle lanes/iter %.2f\n",
+              q[3], (double)q[5] / q[3], (double)q[7] / q[3], q[4], (double)q[6] / q[4], (double)q[8] / (q[3] + q[4]));
+    }
+#endif
   }
   (void)total_samples;
   return RT_OK;
@@ -1062,7 +1069,7 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   const bool count = (flags & RT_COUNTERS) != 0;
   const RtDeviceScene sc = device_scene(s);
   RT_CUDA(cudaMemsetAsync(rs->counters, 0, 28, st));
-  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 64, st));
+  RT_CUDA(cudaMemsetAsync(rs->stats, 0, 128, st));
   pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
   RT_CUDA(cudaEventRecord(rs->e0, st));
   launch_traverse(lane_of(flags), count, rs->trav_grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, 0u, (unsigned)n, rs->trace_hits, rs->counters,

@@ -325,6 +325,9 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
   __shared__ uint2 s_ent[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
   const unsigned lane = threadIdx.x & 31;
   const int tid = threadIdx.x;
+#ifdef RT_LANE_STATS
+  unsigned long long ls_iter[2] = {0, 0}, ls_lanes[2] = {0, 0}, ls_parked = 0, ls_idle = 0;
+#endif
   unsigned long long n_nodes = 0, n_leaves = 0;
   unsigned loc_ref[SUN ? RT_STACK_TOTAL - RT_STACK_SHARED : 1];
   uint2 loc_ent[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
@@ -433,6 +436,14 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       }
     }
     bool need_pop = false;
+#ifdef RT_LANE_STATS  // experiment build only (make EXTRA=-DRT_LANE_STATS, scripts/lane_stats.py): lane occupancy of the two phases
+    if (COUNT && lane == 0) {
+      const bool lp = __popc(leafm) >= RT_LEAF_MIN || leafm == actm;
+      ls_iter[lp ? 1 : 0]++; ls_lanes[lp ? 1 : 0] += lp ? __popc(leafm) : __popc(actm & ~leafm);
+      if (!lp) ls_parked += __popc(leafm);
+      ls_idle += 32 - __popc(actm);
+    }
+#endif
     if (__popc(leafm) >= RT_LEAF_MIN || leafm == actm) {
       // ---- leaf phase ----
       if (atleaf) {
@@ -485,5 +496,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
   if (COUNT) {
     for (int o2 = 16; o2 > 0; o2 >>= 1) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o2); }
     if (lane == 0) { atomicAdd(stats, n_nodes); atomicAdd(stats + 1, n_leaves); }
+#ifdef RT_LANE_STATS
+    if (lane == 0) {
+      atomicAdd(stats + 3, ls_iter[0]); atomicAdd(stats + 4, ls_iter[1]); atomicAdd(stats + 5, ls_lanes[0]); atomicAdd(stats + 6, ls_lanes[1]);
+      atomicAdd(stats + 7, ls_parked); atomicAdd(stats + 8, ls_idle);
+    }
+#endif
   }
 }
