@@ -383,7 +383,8 @@ def run_b200(a):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     traffic = None  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this command
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traverse_r01.json")))["dram_bytes_per_launch_mean"]
+        prof = "ncu_traverse_r01.json" if a.tris == 1_000_000 else "ncu_traverse_%dm_r01.json" % (a.tris // 1_000_000)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", prof)))["dram_bytes_per_launch_mean"]
     except Exception:
         pass
     # per-launch figures: algorithmic bytes of one frame / traverse launches of one frame; duration = live CUDA-event average
@@ -413,7 +414,8 @@ def run_b200(a):
                 "ms_per_step": e2e_res["ms"] / a.steps},
         "gpu_launches": int(dev_res["launches"]),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_note": "dram__bytes_read+write per launch, mean of the 4 launches in profiles/ncu_traverse_r01.json: the ray records in and the hits out; node and leaf fetches hit in L2",
+                     "traffic_note": ("dram__bytes_read+write per launch, mean of the 4 launches in profiles/ncu_traverse_r01.json: the ray records in and the hits out; node and leaf fetches hit in L2"
+                                      if a.tris == 1_000_000 else "dram__bytes_read+write per launch, mean of the launches in profiles/ncu_traverse_%dm_r01.json (null when that capture does not exist)" % (a.tris // 1_000_000)),
                      "kernel": "traverse_near_kernel<EXACT=%d>" % (0 if a.near_first else 1), "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "bytes_per_launch": bytes_per_launch, "ms_per_launch": ms_per_launch,
                      "share_of_step": dev_res["trav_ms"] / dev_res["ms"],

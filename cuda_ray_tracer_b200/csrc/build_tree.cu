@@ -111,6 +111,125 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   }
 }
 
+// ---- fused bottom-up builder, block-local lower levels (RT_BUILD_LOCAL_CLIMB) ---------------------
+// The climb above costs one device-scope exchange and one dependent 32-byte read per level: ~20 L2 round trips
+// in a row per surviving thread.  Here a block owns RT_BU_CHUNK consecutive leaves.  A node whose leaves all lie
+// in the chunk ("local") is completed by this block alone, so its arrival at a parent whose split also lies
+// inside the chunk goes through SHARED memory: deposit the half, one shared exchange, the second child reads the
+// sibling from shared memory and writes the finished 64-byte node to global memory in one piece.  Everything
+// else uses the global protocol of bottom_up_kernel:
+//   * a local node whose parent splits at the chunk border arrives globally right after the local phase;
+//   * a local node left waiting in shared memory when the local phase ends has a sibling that reaches beyond the
+//     chunk (that sibling can only be finished through global arrivals): the thread that owns the slot re-issues
+//     the arrival globally;
+//   * once a thread's node reaches beyond the chunk it stays on the global protocol (ranges only grow).
+// Both children of a split therefore always meet in the same place, and only O(log) nodes per chunk (~3 % at
+// 512 leaves) touch the global flags.  Same tree, same boxes (tests/test_build_gpu.py runs both builders).
+// MEASURED (B200, round 1): 0.320 ms vs 0.309 ms at 1M triangles, 2.36 vs 2.31 ms at 10M — no gain, so the global
+// climb stays the default.  The kernel is bound by the random 2 x 48-byte gather of the primitive records through
+// the sorted permutation (HBM random-gather rate, profiles/l2_peaks_r01.json), not by the arrival atomics.
+#define RT_BU_CHUNK 512
+
+__device__ __forceinline__ float rt_node_aux(const RtBox& b, float slack) {
+  const float cmax = fmaxf(fmaxf(fmaxf(fabsf(b.xmin), fabsf(b.xmax)), fmaxf(fabsf(b.ymin), fabsf(b.ymax))), fmaxf(fabsf(b.zmin), fabsf(b.zmax)));
+  return (slack + 4e-7f * cmax) * 1.000001f;
+}
+
+template <typename KeyT>
+__device__ __forceinline__ void climb_global(const Delta<KeyT>& D, float4* nodes, int* flags, int n, int* root_out, float* root_box,
+                                             int l, int r, RtBox box, uint32_t ref, float slack) {
+  while (true) {
+    if (l == 0 && r == n - 1) {  // root
+      *root_out = (int)ref;
+      root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+      return;
+    }
+    const int dl = D.adj(l - 1), dr = D.adj(r);
+    int s, side, mine;
+    if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
+    store_half(nodes, s, side, box, ref, slack);
+    const int other = exch_acq_rel(flags + s, mine);
+    if (other == -1) return;  // sibling not there yet: it will finish this node
+    RtBox sib;
+    slack = fmaxf(slack, load_half_box(nodes, s, side ^ 1, sib));
+    if (side == 0) { r = other; box = union_box(box, sib); } else { l = other; box = union_box(sib, box); }
+    ref = (uint32_t)s;
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RT_BU_CHUNK) bottom_up_local_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ perm,
+                                                                     const float4* __restrict__ bv, const float4* __restrict__ tv,
+                                                                     float4* __restrict__ sorted_tv, float4* nodes, int* flags, int n,
+                                                                     int* root_out, float* root_box) {
+  __shared__ int s_delta[RT_BU_CHUNK + 1];      // s_delta[i] = delta(c0 - 1 + i, c0 + i)
+  __shared__ int s_flag[RT_BU_CHUNK];           // split after leaf c0 + i: -1 nobody, (range end << 1 | side) one child waits, -2 finished
+  __shared__ float4 s_half[RT_BU_CHUNK][2][2];  // [split][side]: (xmin ymin xmax ymax | zmin zmax ref raw-slack)
+  const int t = threadIdx.x, c0 = blockIdx.x * RT_BU_CHUNK, k = c0 + t;
+  const int c1 = min(c0 + RT_BU_CHUNK, n) - 1;  // last leaf of the chunk
+  Delta<KeyT> D{keys, n};
+  s_delta[t] = D.adj(k - 1);
+  if (t == 0) s_delta[RT_BU_CHUNK] = D.adj(c0 + RT_BU_CHUNK - 1);
+  s_flag[t] = -1;
+  int l = k, r = k;
+  RtBox box; uint32_t ref = 0; float slack = 0.f;
+  if (k < n) {
+    const uint32_t p = perm[k];
+    const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
+    const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+    box = rt_prim_box(a, b, c);
+    float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;  // the trace view in Morton order (leaf k <-> record k)
+    rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.xmax, box.ymax); rec[5] = make_float4(box.zmin, box.zmax, 0.f, 0.f);
+    slack = c.y;  // hit slack of the primitive, computed with the triangle setup (scene.cu, build.cuh)
+    ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
+  }
+  __syncthreads();
+  bool go_global = false;
+  if (k < n) {
+    while (true) {
+      if (l == 0 && r == n - 1) {  // root of a tree that fits one chunk
+        *root_out = (int)ref;
+        root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+        break;
+      }
+      const int dl = s_delta[l - c0], dr = s_delta[r - c0 + 1];
+      int s, side, mine;
+      if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
+      if (s < c0 || s >= c1) { go_global = true; break; }  // the parent splits at the chunk border
+      const int q = s - c0;
+      const float4 h0 = make_float4(box.xmin, box.ymin, box.xmax, box.ymax);
+      s_half[q][side][0] = h0;
+      s_half[q][side][1] = make_float4(box.zmin, box.zmax, __uint_as_float(ref), slack);
+      __threadfence_block();
+      const int other = atomicExch(&s_flag[q], (mine << 1) | side);
+      if (other == -1) break;  // sibling not there yet (or never, in this phase: see the hand-over below)
+      __threadfence_block();
+      const float4 g0 = s_half[q][side ^ 1][0], g1 = s_half[q][side ^ 1][1];
+      RtBox sib; sib.xmin = g0.x; sib.ymin = g0.y; sib.xmax = g0.z; sib.ymax = g0.w; sib.zmin = g1.x; sib.zmax = g1.y;
+      float4* nd = nodes + 4 * (size_t)s;  // the finished node, both halves, one 64-byte line
+      __stcg(nd + 2 * side, h0);
+      __stcg(nd + 2 * side + 1, make_float4(box.zmin, box.zmax, __uint_as_float(ref), rt_node_aux(box, slack)));
+      __stcg(nd + 2 * (side ^ 1), g0);
+      __stcg(nd + 2 * (side ^ 1) + 1, make_float4(g1.x, g1.y, g1.z, rt_node_aux(sib, g1.w)));
+      s_flag[q] = -2;
+      slack = fmaxf(slack, g1.w);
+      if (side == 0) { r = other >> 1; box = union_box(box, sib); } else { l = other >> 1; box = union_box(sib, box); }
+      ref = (uint32_t)s;
+    }
+  }
+  __syncthreads();
+  if (go_global) climb_global(D, nodes, flags, n, root_out, root_box, l, r, box, ref, slack);
+  const int f = s_flag[t];
+  if (f >= 0) {  // a local child of split c0 + t is still waiting: its sibling reaches beyond the chunk
+    const int side = f & 1, end = f >> 1, s = c0 + t;
+    const float4 g0 = s_half[t][side][0], g1 = s_half[t][side][1];
+    RtBox wb; wb.xmin = g0.x; wb.ymin = g0.y; wb.xmax = g0.z; wb.ymax = g0.w; wb.zmin = g1.x; wb.zmax = g1.y;
+    if (side == 0) climb_global(D, nodes, flags, n, root_out, root_box, end, s, wb, __float_as_uint(g1.z), g1.w);
+    else climb_global(D, nodes, flags, n, root_out, root_box, s + 1, end, wb, __float_as_uint(g1.z), g1.w);
+  }
+}
+
 // ---- top-down Karras builder (reference numbering) --------------------------------------------
 template <typename KeyT>
 __global__ void __launch_bounds__(256) karras_topdown_kernel(const KeyT* __restrict__ keys, int n, float4* nodes, int* parent) {
@@ -261,11 +380,17 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
       else karras_topdown_kernel<uint64_t><<<(n - 1 + 255) / 256, 256, 0, st>>>(s->sorted_keys64, n, s->nodes, s->parent);
     }
     refit_kernel<<<grid, 256, 0, st>>>(s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->parent, s->node_flags, n, root_dev, root_box);
-  } else {
+  } else if (!(flags & RT_BUILD_LOCAL_CLIMB)) {
     if (morton_bits == 30)
       bottom_up_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
     else
       bottom_up_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+  } else {
+    const int gl = (n + RT_BU_CHUNK - 1) / RT_BU_CHUNK;
+    if (morton_bits == 30)
+      bottom_up_local_kernel<uint32_t><<<gl, RT_BU_CHUNK, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+    else
+      bottom_up_local_kernel<uint64_t><<<gl, RT_BU_CHUNK, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
   }
   RT_CUDA(cudaGetLastError());
   s->built = true; s->built_bits = morton_bits; s->built_topdown = (flags & RT_BUILD_TOPDOWN) != 0;

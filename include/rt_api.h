@@ -73,8 +73,11 @@ enum {
                                   reference, where every Morton code is 0            */
   RT_BOUNDS_COMPUTED    = 1u,  /* reduce the primitive AABBs on the device (what parse.cpp:147-155,
                                   193-200 accumulates and drops)                                  */
-  RT_BUILD_TOPDOWN      = 2u   /* per-node Karras range/split search (lbvh_builder.cu:103-322) +
+  RT_BUILD_TOPDOWN      = 2u,  /* per-node Karras range/split search (lbvh_builder.cu:103-322) +
                                   separate refit instead of the fused bottom-up builder           */
+  RT_BUILD_LOCAL_CLIMB  = 4u   /* fused bottom-up builder whose levels inside a 512-leaf chunk meet in shared
+                                  memory (default: every level through global atomics); same tree,
+                                  measured no faster (the primitive gather bounds the kernel), kept for A/B */
 };
 int rt_build_lbvh(rt_scene* scene, int morton_bits, unsigned flags, void* stream, float* ms_out);
 /* Device time of the last rt_build_lbvh (the number lbvh_builder.cu:489 prints), read AFTER the fact so

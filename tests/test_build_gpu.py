@@ -30,7 +30,7 @@ def check_build(o, mode, bits, flags_extra=0):
 
 @pytest.mark.parametrize("name", H.SCENES)
 @pytest.mark.parametrize("mode", [O.BOUNDS_SHIPPED, O.BOUNDS_COMPUTED])
-@pytest.mark.parametrize("topdown", [0, api.BUILD_TOPDOWN])
+@pytest.mark.parametrize("topdown", [0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB])
 def test_build_scene_files(name, mode, topdown):
     p = H.scene_path(name)
     if p is None:
@@ -50,7 +50,7 @@ def test_build_computed_bounds_with_host_bounds_in_desc():
     assert np.array_equal(e["codes"], b["codes"]) and np.array_equal(e["perm"], b["perm"])
 
 
-@pytest.mark.parametrize("n", [1, 2, 3, 7, 255, 256, 257, 4095, 4096, 4097, 10000, 100003])
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 255, 256, 257, 511, 512, 513, 1024, 1025, 4095, 4096, 4097, 10000, 100003])
 @pytest.mark.parametrize("bits", [30, 63])
 def test_build_soup_sizes(n, bits):
     cfg, a = synth.soup(n, seed=n, width=32, height=32, aa=0)
@@ -62,7 +62,7 @@ def test_build_soup_sizes(n, bits):
         e = sc.export_reference_layout(bits)
         assert e["nleaf"][0] == 1 and e["perm"][0] == 0
         return
-    for td in (0, api.BUILD_TOPDOWN):
+    for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB):
         check_build(o, O.BOUNDS_COMPUTED, bits, td)
     check_build(o, O.BOUNDS_SHIPPED, bits)
 
@@ -71,7 +71,7 @@ def test_build_mixed_duplicates():
     cfg, a = H.mixed_scene(5000)
     o = H.oracle_from_arrays(cfg, a)
     for bits in (30, 63):
-        for td in (0, api.BUILD_TOPDOWN):
+        for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB):
             check_build(o, O.BOUNDS_COMPUTED, bits, td)
 
 
@@ -81,7 +81,8 @@ def test_build_1m_soup_properties_and_parity():
     a = synth.finish_triangles(a)
     o = H.oracle_from_arrays(cfg, a)
     ms = check_build(o, O.BOUNDS_COMPUTED, 30)
-    print("1M build ms", ms)
+    ms_l = check_build(o, O.BOUNDS_COMPUTED, 30, api.BUILD_LOCAL_CLIMB)
+    print("1M build ms: global climb %.3f, block-local climb %.3f" % (ms, ms_l))
 
 
 def test_sort_is_stable_permutation_vs_torch():
