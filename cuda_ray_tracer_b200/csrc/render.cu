@@ -37,7 +37,7 @@ struct RenderParams {
   int mode;         // 0: aa==0 (exact pixel centre), 1: aa==1 (one jittered sample), 2: aa>=2 (one state per sample)
   int spp;          // samples per pixel actually traced
   int covered;      // pixels [0,covered) are rendered
-  int tile_w, tile_h, tiles_x, num_ranks, rank, slots_per_tile;
+  int tile_w, tile_h, tiles_x, num_ranks, rank, slots_per_tile, sub_w, sub_h;
   int slot0, npix, S;   // this pass: pixel slots [slot0, slot0+npix), S = npix * spp samples
   int depth;        // continuation stack depth (frames per sample)
   int ref_order /* traversal lane, RT_LANE_* */, rough_zyx, need_rng;
@@ -75,12 +75,20 @@ __device__ __forceinline__ int hdr_bounce(unsigned h) { return (int)(short)((h >
 
 // pixel slot -> pixel.  Slots enumerate the rank's tiles (tile t belongs to rank t % num_ranks), row-major
 // inside a tile; slots that fall outside the image (edge tiles) are dead.
+#ifndef RT_SUB_W
+#define RT_SUB_W 8
+#define RT_SUB_H 4
+#endif
 __device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, int slot, int& x, int& y, int& pix) {
   const int lt = slot / P.slots_per_tile, r = slot - lt * P.slots_per_tile;
   const int t = lt * P.num_ranks + P.rank;
   const int tx = t % P.tiles_x, ty = t / P.tiles_x;
-  x = tx * P.tile_w + r % P.tile_w;
-  y = ty * P.tile_h + r / P.tile_w;
+  // inside a tile, slots run over sub_w x sub_h pixel blocks (8 x 4 = one warp) so that the 32 rays of a warp
+  // cover a compact footprint and fetch the same nodes; sub = (tile_w, 1) is plain row-major
+  const int sub = P.sub_w * P.sub_h, blk = r / sub, in = r - blk * sub, bpr = P.tile_w / P.sub_w;
+  const int by = blk / bpr, bx = blk - by * bpr, iy = in / P.sub_w;
+  x = tx * P.tile_w + bx * P.sub_w + (in - iy * P.sub_w);
+  y = ty * P.tile_h + by * P.sub_h + iy;
   pix = y * P.W + x;
   return x < P.W && y < P.H && pix < P.covered;
 }
@@ -89,7 +97,9 @@ __device__ __forceinline__ bool pixel_to_slot(const RenderParams& P, int pix, in
   const int tx = x / P.tile_w, ty = y / P.tile_h;
   const int t = ty * P.tiles_x + tx;
   if (t % P.num_ranks != P.rank) return false;
-  slot = (t / P.num_ranks) * P.slots_per_tile + (y - ty * P.tile_h) * P.tile_w + (x - tx * P.tile_w);
+  const int lx = x - tx * P.tile_w, ly = y - ty * P.tile_h, bx = lx / P.sub_w, by = ly / P.sub_h;
+  slot = (t / P.num_ranks) * P.slots_per_tile + (by * (P.tile_w / P.sub_w) + bx) * (P.sub_w * P.sub_h)
+         + (ly - by * P.sub_h) * P.sub_w + (lx - bx * P.sub_w);
   return true;
 }
 
@@ -876,8 +886,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   const long long ntiles = (long long)P.tiles_x * tiles_y;
   const long long owned = ntiles > P.rank ? (ntiles - P.rank + P.num_ranks - 1) / P.num_ranks : 0;
   P.slots_per_tile = P.tile_w * P.tile_h;
+  if (P.tile_w % RT_SUB_W == 0 && P.tile_h % RT_SUB_H == 0) { P.sub_w = RT_SUB_W; P.sub_h = RT_SUB_H; }
+  else { P.sub_w = P.tile_w; P.sub_h = 1; }
   long long nslots = owned * P.slots_per_tile;
-  if (!tiles) nslots = P.covered;  // one tile = the image: slot == pixel
+  if (!tiles && P.covered < npx) { P.sub_w = P.tile_w; P.sub_h = 1; nslots = P.covered; }  // F3's partial image, one tile: slot == pixel
   P.ref_order = lane_of(flags);
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;

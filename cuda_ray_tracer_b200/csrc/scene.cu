@@ -1,7 +1,7 @@
 // scene.cu — rt_scene_create / destroy / update: upload in the reference's SoA layout, repack on
 // the device into the arena layout described in common.cuh.
 // Replaces src/config_utils.cu:18-232 (≤17 cudaMalloc + pageable cudaMemcpy pairs and a leak of the
-// SoA component arrays, :205-209) by one arena and a handful of bulk copies.
+// SoA component arrays, :205-209) by ONE arena allocation, asynchronous bulk copies staged inside it, one sync.
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -119,15 +119,28 @@ __global__ void update_tris_kernel(int nt, const float* p0a, const float* p1a, c
 
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
-struct TempBuf {  // device staging copy of a caller array (host or device pointer)
-  void* p = nullptr;
-  cudaError_t load(const void* src, size_t bytes) {
+// Upload staging.  The reference marshals with up to 17 cudaMalloc + pageable cudaMemcpy pairs
+// (src/config_utils.cu:72-199).  Here the caller's SoA arrays are copied with cudaMemcpyAsync into ONE staging
+// region — the part of the arena that only the build writes later (sorted leaf records + nodes, 160 B per
+// primitive >= the 116 B per triangle / 60 B per sphere of input) — so scene creation makes exactly one device
+// allocation, never frees anything, and synchronises once.  Arrays that already live in device memory are read in
+// place; pinned host arrays (cudaHostAlloc / cudaHostRegister) go over at full PCIe rate without a bounce copy.
+struct Stager {
+  char* base = nullptr; size_t cap = 0, off = 0;
+  void* overflow = nullptr;  // only when the inputs do not fit the arena scratch (e.g. thousands of planes)
+  cudaError_t place(const void* src, size_t bytes, const void** dev) {
+    *dev = nullptr;
     if (bytes == 0) return cudaSuccess;
-    cudaError_t e = cudaMalloc(&p, bytes);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpy(p, src, bytes, cudaMemcpyDefault);
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged)) { *dev = src; return cudaSuccess; }
+    cudaGetLastError();
+    const size_t need = (bytes + 255) & ~(size_t)255;
+    if (off + need > cap) return cudaErrorMemoryAllocation;
+    *dev = base + off;
+    off += need;
+    return cudaMemcpyAsync(const_cast<void*>(*dev), src, bytes, cudaMemcpyHostToDevice, 0);
   }
-  ~TempBuf() { if (p) cudaFree(p); }
+  ~Stager() { if (overflow) cudaFree(overflow); }
 };
 
 }  // namespace
@@ -186,26 +199,33 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
     cudaFree(s->arena); delete s; return RT_ERR_CUDA;
   };
   {
-    TempBuf sc, sr, sm, t0, t1, t2, tn, te1, te2, tm, planes, flagbuf;
-    const size_t ns = (size_t)s->ns, nt = (size_t)s->nt;
-    if ((e = sc.load(d->sphere_c, ns * 12)) || (e = sr.load(d->sphere_r, ns * 4)) || (e = sm.load(d->sphere_mat, ns * 44)) ||
-        (e = t0.load(d->tri_p0, nt * 12)) || (e = t1.load(d->tri_p1, nt * 12)) || (e = t2.load(d->tri_p2, nt * 12)) ||
-        (e = tn.load(d->tri_nor, nt * 12)) || (e = te1.load(d->tri_e1, nt * 12)) || (e = te2.load(d->tri_e2, nt * 12)) ||
-        (e = tm.load(d->tri_mat, nt * 44)) || (e = planes.load(d->planes, (size_t)d->num_planes * 84)))
-      return fail(e, "upload");
-    if ((e = cudaMalloc(&flagbuf.p, 4)) || (e = cudaMemset(flagbuf.p, 0, 4))) return fail(e, "flags");
-    if (n && (e = cudaMemcpy(s->refs, d->refs, n * 8, cudaMemcpyDefault))) return fail(e, "refs");
-    if (d->num_suns && (e = cudaMemcpy(s->suns, d->suns, (size_t)d->num_suns * 24, cudaMemcpyDefault))) return fail(e, "suns");
-    if (d->num_bulbs && (e = cudaMemcpy(s->bulbs, d->bulbs, (size_t)d->num_bulbs * 24, cudaMemcpyDefault))) return fail(e, "bulbs");
-    if (n) {
-      PackArgs a{(const float*)sc.p, (const float*)sr.p, (const float*)sm.p, (const float*)t0.p, (const float*)t1.p,
-                 (const float*)t2.p, (const float*)tn.p, (const float*)te1.p, (const float*)te2.p, (const float*)tm.p, s->refs, s->n};
-      pack_prims_kernel<<<(unsigned)((n + 255) / 256), 256>>>(a, s->prim_bv, s->prim_tv, s->prim_mat, s->tri_prim, (int*)flagbuf.p);
+    const size_t ns = (size_t)s->ns, nt = (size_t)s->nt, np = (size_t)d->num_planes;
+    Stager S;
+    S.base = A + o_stv; S.cap = (o_nodes + n1 * 64) - o_stv;
+    const size_t need = ns * 60 + nt * 116 + np * 84 + 12 * 256;
+    if (need > S.cap) {  // does not happen for primitive data; a scene with very many planes
+      if ((e = cudaMalloc(&S.overflow, need))) return fail(e, "staging");
+      S.base = (char*)S.overflow; S.cap = need;
     }
-    if (d->num_planes) pack_planes_kernel<<<(d->num_planes + 63) / 64, 64>>>((const float*)planes.p, d->num_planes, s->planes, (int*)flagbuf.p);
-    if ((e = cudaGetLastError()) || (e = cudaDeviceSynchronize())) return fail(e, "pack kernels");
+    const void *sc, *sr, *sm, *t0, *t1, *t2, *tn, *te1, *te2, *tm, *planes;
+    if ((e = S.place(d->sphere_c, ns * 12, &sc)) || (e = S.place(d->sphere_r, ns * 4, &sr)) || (e = S.place(d->sphere_mat, ns * 44, &sm)) ||
+        (e = S.place(d->tri_p0, nt * 12, &t0)) || (e = S.place(d->tri_p1, nt * 12, &t1)) || (e = S.place(d->tri_p2, nt * 12, &t2)) ||
+        (e = S.place(d->tri_nor, nt * 12, &tn)) || (e = S.place(d->tri_e1, nt * 12, &te1)) || (e = S.place(d->tri_e2, nt * 12, &te2)) ||
+        (e = S.place(d->tri_mat, nt * 44, &tm)) || (e = S.place(d->planes, np * 84, &planes)))
+      return fail(e, "upload");
+    int* flagbuf = (int*)(A + o_bnd) + 32;  // spare bytes of the (256-byte aligned) bounds block
+    if ((e = cudaMemsetAsync(flagbuf, 0, 4, 0))) return fail(e, "flags");
+    if (n && (e = cudaMemcpyAsync(s->refs, d->refs, n * 8, cudaMemcpyDefault, 0))) return fail(e, "refs");
+    if (d->num_suns && (e = cudaMemcpyAsync(s->suns, d->suns, (size_t)d->num_suns * 24, cudaMemcpyDefault, 0))) return fail(e, "suns");
+    if (d->num_bulbs && (e = cudaMemcpyAsync(s->bulbs, d->bulbs, (size_t)d->num_bulbs * 24, cudaMemcpyDefault, 0))) return fail(e, "bulbs");
+    if (n) {
+      PackArgs a{(const float*)sc, (const float*)sr, (const float*)sm, (const float*)t0, (const float*)t1,
+                 (const float*)t2, (const float*)tn, (const float*)te1, (const float*)te2, (const float*)tm, s->refs, s->n};
+      pack_prims_kernel<<<(unsigned)((n + 255) / 256), 256>>>(a, s->prim_bv, s->prim_tv, s->prim_mat, s->tri_prim, flagbuf);
+    }
+    if (d->num_planes) pack_planes_kernel<<<(d->num_planes + 63) / 64, 64>>>((const float*)planes, d->num_planes, s->planes, flagbuf);
     int f = 0;
-    if ((e = cudaMemcpy(&f, flagbuf.p, 4, cudaMemcpyDeviceToHost))) return fail(e, "flags readback");
+    if ((e = cudaGetLastError()) || (e = cudaMemcpyAsync(&f, flagbuf, 4, cudaMemcpyDeviceToHost, 0)) || (e = cudaDeviceSynchronize())) return fail(e, "pack kernels");
     s->any_shiny = f & 1; s->any_trans = f & 2; s->any_rough = f & 4;
   }
   if ((e = cudaEventCreate(&s->ev0)) || (e = cudaEventCreate(&s->ev1)) || (e = cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)))

@@ -28,6 +28,37 @@ __global__ void gather_kernel(const float4* buf, unsigned nrec, int steps, float
   }
   if (acc == 1.2345f) out[0] = acc;
 }
+// The same 64-byte records fetched by LANE PAIRS: in one instruction lane 2k reads the first 32 bytes and lane 2k+1
+// the second 32 bytes of ONE record (16 distinct 128-byte lines per warp instruction instead of 32), first for the
+// even lane's record, then for the odd lane's.  L1TEX charges one wavefront per distinct line per instruction
+// (B300_MICROARCH.md, "L1tex wavefront queue"), so the 32 records of a warp cost 32 wavefronts instead of 64.
+// XCHG = 0: each lane keeps the halves it loaded (raw fetch rate).  XCHG = 1: eight shuffles hand every lane its own
+// complete record (what a drop-in replacement of the per-lane fetch costs).
+template <int XCHG>
+__global__ void gather_pair_kernel(const float4* buf, unsigned nrec, int steps, float* out) {
+  unsigned x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+  const unsigned odd = threadIdx.x & 1u;
+  float acc = 0.f;
+  for (int s = 0; s < steps; s++) {
+    x = x * 1664525u + 1013904223u;
+    const unsigned rec = (unsigned)(((unsigned long long)x * nrec) >> 32);
+    const unsigned other = __shfl_xor_sync(0xffffffffu, rec, 1);
+    const unsigned rec_e = odd ? other : rec, rec_o = odd ? rec : other;
+    float4 a, b, c, d;
+    ld256(buf + 4 * (size_t)rec_e + 2 * odd, a, b);   // my half of the even lane's record
+    ld256(buf + 4 * (size_t)rec_o + 2 * odd, c, d);   // my half of the odd lane's record
+    if (XCHG) {  // even lane: keeps (a,b), needs the odd lane's (a,b); odd lane: keeps (c,d), needs the even lane's (c,d)
+      float4 s0 = odd ? a : c, s1 = odd ? b : d;
+      s0.x = __shfl_xor_sync(0xffffffffu, s0.x, 1); s0.y = __shfl_xor_sync(0xffffffffu, s0.y, 1);
+      s0.z = __shfl_xor_sync(0xffffffffu, s0.z, 1); s0.w = __shfl_xor_sync(0xffffffffu, s0.w, 1);
+      s1.x = __shfl_xor_sync(0xffffffffu, s1.x, 1); s1.y = __shfl_xor_sync(0xffffffffu, s1.y, 1);
+      s1.z = __shfl_xor_sync(0xffffffffu, s1.z, 1); s1.w = __shfl_xor_sync(0xffffffffu, s1.w, 1);
+      if (odd) { a = s0; b = s1; } else { c = s0; d = s1; }
+    }
+    acc += a.x + b.w + c.y + d.z;
+  }
+  if (acc == 1.2345f) out[0] = acc;
+}
 int main() {
   const size_t bytes = 64ull << 20;
   float4* buf; float* out; cudaMalloc(&buf, bytes); cudaMalloc(&out, 4); cudaMemset(buf, 0, bytes);
@@ -44,6 +75,15 @@ int main() {
     cudaEventRecord(e0); gather_kernel<<<blocks, tpb>>>(buf, (unsigned)(bytes / 64), steps, out); cudaEventRecord(e1); cudaEventSynchronize(e1);
     cudaEventElapsedTime(&ms, e0, e1);
     printf("L2 gather, 64-byte records at random      : %.0f GB/s (%d x %d threads)\n", (double)blocks * tpb * steps * 64.0 / (ms * 1e-3) / 1e9, blocks, tpb);
+  }
+  for (int v = 0; v < 2; v++) {
+    const int blocks = sms * 16, steps = 2000, tpb = 128;
+    if (v) gather_pair_kernel<1><<<blocks, tpb>>>(buf, (unsigned)(bytes / 64), 100, out); else gather_pair_kernel<0><<<blocks, tpb>>>(buf, (unsigned)(bytes / 64), 100, out);
+    cudaEventRecord(e0);
+    if (v) gather_pair_kernel<1><<<blocks, tpb>>>(buf, (unsigned)(bytes / 64), steps, out); else gather_pair_kernel<0><<<blocks, tpb>>>(buf, (unsigned)(bytes / 64), steps, out);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    printf("L2 gather, 64-byte records, lane pairs%s: %.0f GB/s\n", v ? " + 8 shuffles" : " (no exchange)", (double)blocks * tpb * steps * 64.0 / (ms * 1e-3) / 1e9);
   }
   // the same gather from an array that does not fit L2 (1 GB): HBM-bound
   cudaFree(buf); const size_t big = 1ull << 30; cudaMalloc(&buf, big); cudaMemset(buf, 0, big);
