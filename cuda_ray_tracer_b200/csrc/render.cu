@@ -721,11 +721,12 @@ struct RngTables {  // device copies of the skip-ahead matrices, one set per dev
 };
 
 struct RenderState {
-  char* pool = nullptr; size_t pool_bytes = 0;
-  uint32_t* counters = nullptr; unsigned long long* stats = nullptr;
-  uint32_t* h_count = nullptr;  // pinned
+  char* pool[2] = {nullptr, nullptr}; size_t pool_bytes[2] = {0, 0};  // one per pass in flight
+  uint32_t* counters = nullptr; unsigned long long* stats = nullptr;  // counters: 16 words per pass context
+  uint32_t* h_count = nullptr;  // pinned, 16 words per pass context
   RngTables rng;
-  cudaEvent_t e0 = nullptr, e1 = nullptr, t0 = nullptr, t1 = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr, t0[2] = {nullptr, nullptr}, t1[2] = {nullptr, nullptr}, ev_cnt[2] = {nullptr, nullptr};
+  cudaStream_t pass_stream = nullptr; cudaEvent_t ev_fork2 = nullptr, ev_join2 = nullptr;  // second pass in flight
   cudaStream_t head_stream = nullptr; cudaEvent_t ev_join = nullptr;  // RT_RENDER_OVERLAP_BUILD
   int trav_grid = 0;
   uint8_t* d_rgba = nullptr; int32_t* d_ids = nullptr; uint8_t* d_written = nullptr; size_t img_px = 0;  // rt_render_host staging
@@ -739,11 +740,14 @@ RenderState* get_state(rt_scene* s) {
 
 int ensure_common(rt_scene* s, RenderState* st) {
   if (!st->counters) {
-    RT_CUDA(cudaMalloc(&st->counters, 64));
+    RT_CUDA(cudaMalloc(&st->counters, 128));
     RT_CUDA(cudaMalloc(&st->stats, 128));
-    RT_CUDA(cudaMallocHost(&st->h_count, 64));
+    RT_CUDA(cudaMallocHost(&st->h_count, 128));
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
-    RT_CUDA(cudaEventCreate(&st->t0)); RT_CUDA(cudaEventCreate(&st->t1));
+    for (int k = 0; k < 2; k++) {
+      RT_CUDA(cudaEventCreate(&st->t0[k])); RT_CUDA(cudaEventCreate(&st->t1[k]));
+      RT_CUDA(cudaEventCreateWithFlags(&st->ev_cnt[k], cudaEventDisableTiming));
+    }
     int per_sm = 0, sms = 0;
     RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
@@ -839,10 +843,14 @@ size_t env_size(const char* name, size_t dflt) {
 int rt_render_free_state(rt_scene* s) {
   RenderState* st = (RenderState*)s->rstate;
   if (!st) return RT_OK;
-  cudaFree(st->pool); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
+  cudaFree(st->pool[0]); cudaFree(st->pool[1]); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
   cudaFree(st->rng.mats); cudaFree(st->rng.nib); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
   cudaFree(st->trace_q); cudaFree(st->trace_hits); cudaFree(st->trace_fb);
-  if (st->e0) { cudaEventDestroy(st->e0); cudaEventDestroy(st->e1); cudaEventDestroy(st->t0); cudaEventDestroy(st->t1); }
+  if (st->e0) {
+    cudaEventDestroy(st->e0); cudaEventDestroy(st->e1);
+    for (int k = 0; k < 2; k++) { cudaEventDestroy(st->t0[k]); cudaEventDestroy(st->t1[k]); cudaEventDestroy(st->ev_cnt[k]); }
+  }
+  if (st->pass_stream) { cudaStreamDestroy(st->pass_stream); cudaEventDestroy(st->ev_fork2); cudaEventDestroy(st->ev_join2); }
   if (st->head_stream) { cudaStreamDestroy(st->head_stream); cudaEventDestroy(st->ev_join); }
   delete st;
   s->rstate = nullptr;
@@ -908,7 +916,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (P.mode == 2) { rc = ensure_rng_tables(rs, std::max(32, P.spp), 0); if (rc) return rc; }
   else if (P.need_rng) { rc = ensure_rng_tables(rs, 256, (int)((npx + 255) / 256)); if (rc) return rc; }
 
-  // pass size: all per-sample state lives in one pool
+  // pass size: all per-sample state of a pass lives in one pool (RT_POOL_BYTES each, default 6 GB)
   const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8 + 4;
   const size_t budget = env_size("RT_POOL_BYTES", (size_t)6 << 30);
   const long long total_samples = nslots * P.spp;
@@ -916,29 +924,57 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   long long npix_pass = std::max<long long>(1, max_s / P.spp);
   if (npix_pass >= nslots) npix_pass = nslots;
   else npix_pass = std::max<long long>(32, npix_pass & ~31ll);
-  if (nslots == 0) npix_pass = 0;
+  // TWO PASSES IN FLIGHT.  Every traverse launch pays ~0.46 ms whatever its size (scripts/launch_fixed_cost.py): the
+  // kernel cannot end before its longest rays have, a ray is a chain of dependent node fetches, and the longest of
+  // 25 M rays is ~30x the mean, so the last ~0.4 ms of a launch keep a handful of warps busy on an otherwise empty
+  // GPU.  Passes are independent (disjoint pixels), so two of them run on two streams with a pool each: while one
+  // pass drains, the CTAs of the other pass's kernels fill the SMs it leaves.  The host alternates between the two
+  // (it blocks on one pass's ray counts while the other pass's kernels are queued), so neither stream runs dry.  A
+  // frame that fits one pass is split in two for the same reason.  Same pixels: a pass is the same computation on
+  // whichever stream it runs (tests/test_render_gpu.py::test_multi_pass_equals_single_pass and the parity suite).
+  const bool serial = (flags & RT_RENDER_SERIAL_PASSES) != 0 || getenv("RT_SERIAL_PASSES") != nullptr;
+  const int nctx = (!serial && total_samples >= (1ll << 21)) ? 2 : 1;
+  if (nslots > 0) {  // balanced passes (an even number of them when two are in flight)
+    long long npass = (nslots + npix_pass - 1) / npix_pass;
+    if (nctx == 2) npass = (npass + 1) & ~1ll;
+    npix_pass = std::min<long long>(nslots, std::max<long long>(32, ((nslots + npass - 1) / npass + 31) & ~31ll));
+  } else npix_pass = 0;
   const size_t Smax = (size_t)npix_pass * P.spp;
   auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
   const size_t need = al(Smax * 16) * 2 + al(Smax * 16) + al(Smax * 4) + al(Smax * 64 * P.depth) + al(Smax * 32) * 2 + al(Smax * 8) + al(Smax * 4) + 4096;
-  if (need > rs->pool_bytes) {
-    if (rs->pool) cudaFree(rs->pool);
-    rs->pool = nullptr; rs->pool_bytes = 0;
-    cudaError_t e = cudaMalloc((void**)&rs->pool, need);
-    if (e != cudaSuccess) { rt_set_error(std::string("rt_render: state pool cudaMalloc: ") + cudaGetErrorString(e)); return RT_ERR_NOMEM; }
-    rs->pool_bytes = need;
+  const RtDeviceScene sc = device_scene(s);
+  struct PassCtx {
+    RenderBuffers B; RenderParams P; cudaStream_t st = nullptr; uint32_t* counters = nullptr; uint32_t* h_count = nullptr;
+    cudaEvent_t ev_cnt = nullptr, t0 = nullptr, t1 = nullptr;
+    bool active = false, after_gen = false; unsigned n_front = 0, n_back = 0; float4 *qin = nullptr, *qout = nullptr; int iter_in_pass = 0;
+  } ctx[2];
+  if (nctx == 2 && !rs->pass_stream) {
+    RT_CUDA(cudaStreamCreateWithFlags(&rs->pass_stream, cudaStreamNonBlocking));
+    RT_CUDA(cudaEventCreateWithFlags(&rs->ev_fork2, cudaEventDisableTiming));
+    RT_CUDA(cudaEventCreateWithFlags(&rs->ev_join2, cudaEventDisableTiming));
   }
-  RenderBuffers B; memset(&B, 0, sizeof(B));
-  {
-    char* p = rs->pool;
+  for (int k = 0; k < nctx; k++) {
+    if (need > rs->pool_bytes[k]) {
+      if (rs->pool[k]) cudaFree(rs->pool[k]);
+      rs->pool[k] = nullptr; rs->pool_bytes[k] = 0;
+      cudaError_t e = cudaMalloc((void**)&rs->pool[k], need);
+      if (e != cudaSuccess) { rt_set_error(std::string("rt_render: state pool cudaMalloc: ") + cudaGetErrorString(e)); return RT_ERR_NOMEM; }
+      rs->pool_bytes[k] = need;
+    }
+    PassCtx& c = ctx[k];
+    RenderBuffers& B = c.B; memset(&B, 0, sizeof(B));
+    char* p = rs->pool[k];
     B.rng0 = (uint4*)p; p += al(Smax * 16); B.rng1 = (uint4*)p; p += al(Smax * 16);
     B.accum = (float4*)p; p += al(Smax * 16); B.ctl = (uint32_t*)p; p += al(Smax * 4);
     B.frames = (float4*)p; p += al(Smax * 64 * P.depth);
     B.qa = (float4*)p; p += al(Smax * 32); B.qb = (float4*)p; p += al(Smax * 32);
     B.hits = (float2*)p; p += al(Smax * 8);
     B.fb_list = (unsigned*)p; p += al(Smax * 4);
+    c.counters = rs->counters + 16 * k; c.h_count = rs->h_count + 16 * k;
+    B.counters = c.counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
+    c.st = k == 0 ? st : rs->pass_stream;
+    c.ev_cnt = rs->ev_cnt[k]; c.t0 = rs->t0[k]; c.t1 = rs->t1[k];
   }
-  B.counters = rs->counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
-  const RtDeviceScene sc = device_scene(s);
 
   // The head of the frame (clears, RNG seeding and primary ray generation of the first pass) reads nothing the build
   // writes.  With RT_RENDER_OVERLAP_BUILD it runs on its own stream from the point in `st` before this frame's
@@ -959,65 +995,103 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, hs));
   if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, hs));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 128, hs));
-  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 64, hs));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 128, hs));
+  if (nctx == 2) {  // the second pass stream starts after the caller's work on `st` (the build) and after the clears
+    RT_CUDA(cudaEventRecord(rs->ev_fork2, st));
+    RT_CUDA(cudaStreamWaitEvent(rs->pass_stream, rs->ev_fork2, 0));
+    if (hs != st) {
+      RT_CUDA(cudaEventRecord(rs->ev_join2, hs));
+      RT_CUDA(cudaStreamWaitEvent(rs->pass_stream, rs->ev_join2, 0));
+    }
+  }
   uint64_t rays = 0, samples = 0; uint32_t iters = 0, passes = 0, launches = 0; float trav_ms = 0.f; uint64_t fb_rays = 0; uint32_t trav_launches = 0;
-  for (long long slot0 = 0; slot0 < nslots; slot0 += npix_pass) {
-    P.slot0 = (int)slot0; P.npix = (int)std::min<long long>(npix_pass, nslots - slot0); P.S = P.npix * P.spp;
+  long long next_slot0 = 0;
+  bool head_joined = (hs == st);
+  int err = RT_OK;
+#define RT_PASS_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rt_set_error(std::string("rt_render: ") + cudaGetErrorString(e_)); return RT_ERR_CUDA; } } while (0)
+  // queue the head of the next pass (RNG seeding, primary rays) on context c and ask for its ray count
+  auto start_pass = [&](PassCtx& c) -> int {
+    c.P = P;
+    c.P.slot0 = (int)next_slot0; c.P.npix = (int)std::min<long long>(npix_pass, nslots - next_slot0); c.P.S = c.P.npix * c.P.spp;
+    next_slot0 += npix_pass;
     passes++;
-    samples += (uint64_t)P.S;
-    RT_CUDA(cudaMemsetAsync(rs->counters, 0, 8, hs));
-    if (P.mode != 2 && P.need_rng) {
+    samples += (uint64_t)c.P.S;
+    // the very first pass of the frame may run its head on the build-overlap stream
+    cudaStream_t gs = (!head_joined && c.st == st) ? hs : c.st;
+    RT_PASS_CUDA(cudaMemsetAsync(c.counters, 0, 8, gs));
+    if (c.P.mode != 2 && c.P.need_rng) {
       const int hn = (int)(((npx + 255) / 256 + 31) & ~31ll);
-      rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, hs>>>(P, B, hn);
+      rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, gs>>>(c.P, c.B, hn);
       launches++;
     }
-    generate_kernel<<<(unsigned)((P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, hs>>>(P, B, B.qa, d_hit_id);
+    generate_kernel<<<(unsigned)((c.P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, gs>>>(c.P, c.B, c.B.qa, d_hit_id);
     launches++;
-    RT_CUDA(cudaGetLastError());
-    if (hs != st) {  // join: everything below is ordered after both the build and the head
-      RT_CUDA(cudaEventRecord(rs->ev_join, hs));
-      RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join, 0));
-      hs = st;
+    RT_PASS_CUDA(cudaGetLastError());
+    if (gs != c.st) {  // join: everything below is ordered after both the build and the head
+      RT_PASS_CUDA(cudaEventRecord(rs->ev_join, gs));
+      RT_PASS_CUDA(cudaStreamWaitEvent(c.st, rs->ev_join, 0));
+      head_joined = true;
     }
-    RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 4, cudaMemcpyDeviceToHost, st));
-    RT_CUDA(cudaStreamSynchronize(st));
-    unsigned n_front = rs->h_count[0], n_back = 0;  // primary rays all go to the front end
-    float4 *qin = B.qa, *qout = B.qb;
-    int iter_in_pass = 0;
-    while (n_front + n_back > 0) {
+    RT_PASS_CUDA(cudaMemcpyAsync(c.h_count, c.counters + 1, 4, cudaMemcpyDeviceToHost, c.st));
+    RT_PASS_CUDA(cudaEventRecord(c.ev_cnt, c.st));
+    c.active = true; c.after_gen = true; c.qin = c.B.qa; c.qout = c.B.qb; c.iter_in_pass = 0;
+    return RT_OK;
+  };
+  // the ray counts context c asked for are in: queue its next wavefront iteration, or finish the pass and start another
+  auto advance = [&](PassCtx& c) -> int {
+    RT_PASS_CUDA(cudaEventSynchronize(c.ev_cnt));
+    if (c.after_gen) { c.n_front = c.h_count[0]; c.n_back = 0; c.after_gen = false; }  // primary rays all go to the front end
+    else {
+      fb_rays += c.h_count[2];
+      if (time_trav) { float ms = 0.f; RT_PASS_CUDA(cudaEventElapsedTime(&ms, c.t0, c.t1)); trav_ms += ms; }
+      c.n_front = c.h_count[0]; c.n_back = c.h_count[4];
+      if (c.h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
+      std::swap(c.qin, c.qout);
+    }
+    const unsigned n_front = c.n_front, n_back = c.n_back;
+    if (n_front + n_back > 0) {
       iters++; rays += (uint64_t)n_front + n_back;
-      RT_CUDA(cudaMemsetAsync(rs->counters, 0, 28, st));
-      if (time_trav) RT_CUDA(cudaEventRecord(rs->t0, st));
-      const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, st, sc, (const float4*)qin, n_front, n_back, (unsigned)P.S, B.hits,
-                                     rs->counters, rs->stats, B.fb_list);
+      RT_PASS_CUDA(cudaMemsetAsync(c.counters, 0, 28, c.st));
+      if (time_trav) RT_PASS_CUDA(cudaEventRecord(c.t0, c.st));
+      const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, c.st, sc, (const float4*)c.qin, n_front, n_back, (unsigned)c.P.S, c.B.hits,
+                                     c.counters, rs->stats, c.B.fb_list);
       launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
-      if (time_trav) RT_CUDA(cudaEventRecord(rs->t1, st));
+      if (time_trav) RT_PASS_CUDA(cudaEventRecord(c.t1, c.st));
       {
         const unsigned sg = (n_front + n_back + 127) / 128;
-        const bool first = iter_in_pass == 0;
-        if (P.full_shade) { if (first) shade_kernel<true, true><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
-                            else shade_kernel<true, false><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id); }
-        else { if (first) shade_kernel<false, true><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id);
-               else shade_kernel<false, false><<<sg, 128, 0, st>>>(P, sc, B, qin, n_front, n_back, qout, d_hit_id); }
-        iter_in_pass++;
+        const bool first = c.iter_in_pass == 0;
+        if (P.full_shade) { if (first) shade_kernel<true, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id);
+                            else shade_kernel<true, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id); }
+        else { if (first) shade_kernel<false, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id);
+               else shade_kernel<false, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id); }
+        c.iter_in_pass++;
       }
       launches++;
-      RT_CUDA(cudaGetLastError());
-      RT_CUDA(cudaMemcpyAsync(rs->h_count, rs->counters + 1, 20, cudaMemcpyDeviceToHost, st));
-      RT_CUDA(cudaStreamSynchronize(st));
-      fb_rays += rs->h_count[2];
-      if (time_trav) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->t0, rs->t1)); trav_ms += ms; }
-      n_front = rs->h_count[0]; n_back = rs->h_count[4];
-      if (rs->h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
-      std::swap(qin, qout);
+      RT_PASS_CUDA(cudaGetLastError());
+      RT_PASS_CUDA(cudaMemcpyAsync(c.h_count, c.counters + 1, 20, cudaMemcpyDeviceToHost, c.st));
+      RT_PASS_CUDA(cudaEventRecord(c.ev_cnt, c.st));
+      return RT_OK;
     }
-    resolve_kernel<<<(P.npix + 127) / 128, 128, 0, st>>>(P, B, d_rgba, d_written);
+    resolve_kernel<<<(c.P.npix + 127) / 128, 128, 0, c.st>>>(c.P, c.B, d_rgba, d_written);
     launches++;
-    RT_CUDA(cudaGetLastError());
-  }
-  if (hs != st) {  // nothing to render: the clears still belong to this call
+    RT_PASS_CUDA(cudaGetLastError());
+    c.active = false;
+    if (next_slot0 < nslots) return start_pass(c);
+    return RT_OK;
+  };
+  for (int k = 0; k < nctx && err == RT_OK && next_slot0 < nslots; k++) err = start_pass(ctx[k]);
+  while (err == RT_OK && (ctx[0].active || ctx[1].active))
+    for (int k = 0; k < nctx && err == RT_OK; k++)
+      if (ctx[k].active) err = advance(ctx[k]);
+#undef RT_PASS_CUDA
+  if (err != RT_OK) { const std::string keep = rt_last_error(); cudaDeviceSynchronize(); rt_set_error(keep); return err; }  // nothing of this frame stays in flight
+  if (!head_joined) {  // nothing to render: the clears still belong to this call
     RT_CUDA(cudaEventRecord(rs->ev_join, hs));
     RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join, 0));
+  }
+  if (nctx == 2) {  // the caller's stream continues after both pass streams
+    RT_CUDA(cudaEventRecord(rs->ev_join2, rs->pass_stream));
+    RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join2, 0));
   }
   RT_CUDA(cudaEventRecord(rs->e1, st));
   RT_CUDA(cudaEventSynchronize(rs->e1));

@@ -116,6 +116,16 @@ __device__ __forceinline__ void rt_ld256(const float4* p, float4& a, float4& b) 
                : "l"(p));
 }
 
+// the same load executed only where `on` (the destination registers keep whatever they held otherwise)
+__device__ __forceinline__ void rt_ld256_if(const float4* p, const bool on, float4& a, float4& b) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %9, 0;\n\t@p ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p), "r"((unsigned)on));
+}
+#ifndef RT_PAIR_FETCH
+#define RT_PAIR_FETCH 0
+#endif
+
 // primitive test at sorted position k; returns true and the distance when the reference's test reports a hit.
 // Leaf records are 64 bytes: (p0.xyz nor.x | nor.yz e1.xy) (e1.z e2.xyz | file-order index, 0, 0, 0)
 __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, const unsigned ref, const V3 o, const V3 d, float& th) {
@@ -403,6 +413,8 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       }
       if (!exhausted) {
         if (chunk_next == chunk_end) {
+          // (Guided chunk sizes — ever smaller pieces towards the end of the queue — were measured: no change of the
+          // per-launch fixed cost, which is the latency of the longest single rays, scripts/launch_fixed_cost.py.)
           unsigned base = 0;
           if (lane == 0) base = atomicAdd(fetch_counter, (unsigned)RT_CHUNK);
           base = __shfl_sync(0xffffffffu, base, 0);
@@ -444,13 +456,65 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       ls_idle += 32 - __popc(actm);
     }
 #endif
-    if (__popc(leafm) >= RT_LEAF_MIN || leafm == actm) {
+    // (Serving leaf lanes AND node lanes in every iteration once the queue is empty — latency over throughput in the
+    // drain — was measured: no change of the per-launch fixed cost, scripts/launch_fixed_cost.py.)
+    const bool leaf_phase = __popc(leafm) >= RT_LEAF_MIN || leafm == actm;
+    if (leaf_phase) {
       // ---- leaf phase ----
       if (atleaf) {
         RT_LEAF_TEST(cur);
         if (((SUN || (fl & F_ANYHIT)) && best >= 0) || (fl & F_FALLBACK)) st = DONE; else need_pop = true;
       }
-    } else if (act && !atleaf) {
+    }
+#if RT_PAIR_FETCH
+    else {
+      // ---- node phase, node fetched by LANE PAIRS ----
+      // EXPERIMENT, off by default.  Measured on the 4K soup frame: 2579-2813 Mrays/s against 3410 (-18 % .. -25 %) at
+      // 72 / 64 / 56 registers: halving the L1TEX wavefronts does not pay for 9 shuffles + 16 selects per node step
+      // and 16 more live registers in a kernel that issues at 70 %.
+      // L1TEX charges one wavefront per distinct 128-byte line per load instruction, so 32 lanes reading 32 different
+      // nodes cost 32 wavefronts per 32-byte half.  Here lanes 2k and 2k+1 read the two halves of ONE node in the same
+      // instruction (first the even lane's node, then the odd lane's): 16 lines per instruction, half the wavefronts
+      // per node (scripts/microbench/l2bw.cu: 14.7 instead of 8.2 TB/s of 64-byte records).  Each lane keeps the half
+      // of its own node that it loaded itself (child A: the left child on even lanes, the right child on odd lanes)
+      // and receives the other half (child B) from its partner through eight shuffles.
+      const bool step = act && !atleaf;
+      const unsigned odd = lane & 1u;
+      const unsigned mine = step ? cur : 0xFFFFFFFFu;
+      const unsigned theirs = __shfl_xor_sync(0xffffffffu, mine, 1);
+      const unsigned ce = odd ? theirs : mine, co = odd ? mine : theirs;
+      float4 x0, x1, y0, y1;
+      rt_ld256_if(sc.nodes + 4 * (size_t)ce + 2 * odd, ce != 0xFFFFFFFFu, x0, x1);
+      rt_ld256_if(sc.nodes + 4 * (size_t)co + 2 * odd, co != 0xFFFFFFFFu, y0, y1);
+      float4 a0 = odd ? y0 : x0, a1 = odd ? y1 : x1, b0 = odd ? x0 : y0, b1 = odd ? x1 : y1;
+      b0.x = __shfl_xor_sync(0xffffffffu, b0.x, 1); b0.y = __shfl_xor_sync(0xffffffffu, b0.y, 1);
+      b0.z = __shfl_xor_sync(0xffffffffu, b0.z, 1); b0.w = __shfl_xor_sync(0xffffffffu, b0.w, 1);
+      b1.x = __shfl_xor_sync(0xffffffffu, b1.x, 1); b1.y = __shfl_xor_sync(0xffffffffu, b1.y, 1);
+      b1.z = __shfl_xor_sync(0xffffffffu, b1.z, 1);
+      if (EXACT && !SUN) b1.w = __shfl_xor_sync(0xffffffffu, b1.w, 1);
+      if (step) {
+        if (COUNT) n_nodes++;
+        float ea, eb;
+        V3 tna, tnb;
+        bool ha = rt_slab_tn2<true>(a0, a1, q2, (EXACT || SUN) ? INFINITY : tmax, ea, tna);
+        bool hb = rt_slab_tn2<true>(b0, b1, q2, (EXACT || SUN) ? INFINITY : tmax, eb, tnb);
+        const unsigned refa = __float_as_uint(a1.z), refb = __float_as_uint(b1.z);
+        float ka = ea, kb = eb;
+        if (EXACT && !SUN) {
+          const V3 inv = rt_ray2_inv(q2);
+          ka = rt_key_inflated(tna, a1.w, inv, omk); kb = rt_key_inflated(tnb, b1.w, inv, omk);
+          ha = ha && !(ka > tcut); hb = hb && !(kb > tcut);
+        }
+        // the order of the scalar kernel: right child first iff it is hit and (the left is not, or right enters strictly
+        // earlier).  Even lanes: A = left, B = right.  Odd lanes: A = right, B = left.
+        const bool b_first = hb && (!ha || (odd ? !(ea < eb) : (eb < ea)));
+        if (ha && hb) RT_PUSH(b_first ? refa : refb, b_first ? ka : kb);
+        cur = b_first ? refb : refa;
+        need_pop = !(ha || hb);
+      }
+    }
+#else
+    if (!leaf_phase && act && !atleaf) {
       // ---- node phase ----
       if (COUNT) n_nodes++;
       const float4* np = sc.nodes + 4 * (size_t)cur;
@@ -476,6 +540,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       cur = right_first ? refr : refl;
       need_pop = !(hl || hr);
     }
+#endif
     // ---- next position from the stack, skipping entries the current hit has made unreachable ----
     if (need_pop) {
       st = DONE;

@@ -110,7 +110,7 @@ enum {
   RT_TIME_TRAVERSE    = 16u,  /* fill traverse_ms (CUDA events around the traverse launches) only  */
   RT_TRAVERSE_REF_ORDER = 32u, /* every ray in the reference's left-first visiting order
                                  (bvh_traversal.cu:149-179): the exact lane's fallback, for all rays */
-  RT_RENDER_OVERLAP_BUILD = 64u /* frame loops (update -> build -> render on ONE stream): run the part of the
+  RT_RENDER_OVERLAP_BUILD = 64u, /* frame loops (update -> build -> render on ONE stream): run the part of the
                                  frame that does not read the BVH (image clear, primary ray generation of the
                                  first pass) on an internal stream that forks from `stream` at the frame's
                                  first rt_scene_update_triangles / rt_build_lbvh call, i.e. concurrently with
@@ -118,6 +118,10 @@ enum {
                                  that call touches the render's output buffers.  Same pixels either way.
                                  rt_scene_begin_frame moves the fork point earlier (e.g. before the caller's
                                  own vertex upload)                                                        */
+  RT_RENDER_SERIAL_PASSES = 128u /* one pass at a time on `stream` alone.  Default: two passes in flight on two
+                                 streams with a state pool each, so that the drain of one pass's kernels (its
+                                 longest rays) overlaps the other pass's work; traverse_ms then adds up launch
+                                 durations that overlap each other.  Same pixels either way.               */
 };
 int rt_scene_begin_frame(rt_scene* scene, void* stream);
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
