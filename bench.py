@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=16)
     ap.add_argument("--near-first", action="store_true", help="RT_TRAVERSE_NEAR_FIRST lane (not bit-exact in rare cases)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--overlap-build", action="store_true", help="device leg: RT_RENDER_OVERLAP_BUILD (the frame's ray generation runs beside update+build), as the e2e leg always does")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_gpu_fast) on this GPU")
     return ap.parse_args()
@@ -60,44 +61,52 @@ def frame_vertices(arrays, frame):
     return (p0 + d).astype(np.float32), (p1 + d).astype(np.float32), (p2 + d).astype(np.float32)
 
 
-class ClockSampler(threading.Thread):
-    """SM clock and throttle reasons sampled DURING the timed region: NVML every 20 ms (nvidia-smi, the recipe's
-    command, as the fallback: it needs ~100 ms per query, too slow for a sub-second timed region)."""
+class ClockSampler:
+    """SM clock and throttle reasons of the timed region.  NVML is queried in this process BETWEEN the timed steps:
+    right after a step's closing synchronize (the GPU has just been under load for the whole step, the clock domain has
+    not moved yet) and before the L2 flush, i.e. inside the timed loop but outside every CUDA-event interval.
+    A concurrent sampler (a thread polling NVML every 20 ms, or a helper process every 25 ms) was measured to
+    slow a 7.5 ms frame to 8.3 - 13.8 ms: NVML calls contend with the render loop's CUDA calls for driver locks, and
+    the loop waits on the host several times per pass.  Fallback without pynvml: nvidia-smi (the recipe's clocks
+    line) at the same points, first and last step only (it needs ~100 ms per query)."""
     REASONS = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index = index; self.sm = []; self.mx = []; self.mask = 0; self.stop_flag = False; self.how = "nvml"
-
-    def run(self):
+        self.index = index; self.sm = []; self.mx = []; self.mask = 0; self.how = "nvml, after every timed step"; self.h = None; self.calls = 0
         try:
             import pynvml
             pynvml.nvmlInit()
-            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
-            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)))
-            while not self.stop_flag:
-                self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
-                try:
-                    self.mask |= int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
-                except Exception:
-                    self.mask |= int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
-                time.sleep(0.02)
-            return
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)))
         except Exception:
-            self.how = "nvidia-smi"
-        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
-        while not self.stop_flag:
+            self.h = None; self.how = "nvidia-smi, after the first and the last timed step"
+
+    def sample(self, last=False):
+        self.calls += 1
+        if self.h is not None:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                r = [x.strip() for x in out.split(",")]
-                self.sm.append(float(r[0])); self.mx.append(float(r[1]))
-                for k, (_, bit) in enumerate(self.REASONS):
-                    if r[2 + k].lower().startswith("active"):
-                        self.mask |= bit
+                self.sm.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                try:
+                    self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
             except Exception:
                 pass
-            time.sleep(0.05)
+            return
+        if self.calls > 1 and not last:
+            return
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=5).stdout.strip()
+            r = [x.strip() for x in out.split(",")]
+            self.sm.append(float(r[0])); self.mx.append(float(r[1]))
+            for k, (_, bit) in enumerate(self.REASONS):
+                if r[2 + k].lower().startswith("active"):
+                    self.mask |= bit
+        except Exception:
+            pass
 
     def summary(self):
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
@@ -250,6 +259,7 @@ def run_b200(a):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     api.load_library()  # raises when libb200rt.so is missing: there is no fallback
+    sampler = ClockSampler(local) if (rank == 0 and not os.environ.get("BENCH_NO_SAMPLER")) else None
 
     cfg, arrays = synth.soup(a.tris, 1, a.width, a.height, a.spp)
     W, Hh, spp, n = a.width, a.height, a.spp, a.tris
@@ -273,7 +283,7 @@ def run_b200(a):
     img_h = torch.zeros((Hh, W, 4), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tiles = parallel.tile_set(world, rank, width=W)
-    rflags = api.SPP_TRUE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0)
+    rflags = api.SPP_TRUE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0) | (api.RENDER_OVERLAP_BUILD if a.overlap_build else 0)
     # launch durations of the dominant kernel (roofline) are taken with one pass at a time: with two passes in flight
     # (the default, and what `value` and `e2e` run) a launch's event interval includes waiting for the other pass's CTAs
     rflags_serial = rflags | api.TIME_TRAVERSE | api.RENDER_SERIAL_PASSES
@@ -317,7 +327,7 @@ def run_b200(a):
             sc.render_host_into(img_h, W, Hh, spp, flags=rflags_e2e, counters=cnt)
         return sc.build_ms()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, smp=None):
         cnt = api.Counters()
         for f in range(warmup):
             fn(f, cnt); flush.fill_(f & 255)
@@ -325,12 +335,15 @@ def run_b200(a):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
         ms = []; rays = 0; bms = []; trav_ms = 0.0; trav_launches = 0; launches = 0
         for f in range(steps):
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
             e0.record()
             b = fn(warmup + f, cnt)
             e1.record(); torch.cuda.synchronize()
+            if smp is not None:
+                smp.sample(last=(f == steps - 1))  # between the timed intervals: see ClockSampler
             ms.append(e0.elapsed_time(e1)); bms.append(b); rays += cnt.rays
             trav_ms += cnt.traverse_ms; trav_launches += cnt.traverse_launches; launches += cnt.kernel_launches + BUILD_LAUNCHES
             flush.fill_(f & 255)  # L2 flush between timed iterations (256 MiB > 126 MB L2), outside the timed events
@@ -342,14 +355,10 @@ def run_b200(a):
         if world > 1:
             mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
             sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-            return dict(ms=mx[0].item(), rays=sm[1].item(), trav_ms=mx[2].item(), trav_launches=t[3].item(), launches=sm[4].item(), build_ms=mx[5].item() / steps)
-        return dict(ms=total_ms, rays=float(rays), trav_ms=trav_ms, trav_launches=float(trav_launches), launches=float(launches), build_ms=sum(bms) / steps)
+            return dict(ms=mx[0].item(), rays=sm[1].item(), trav_ms=mx[2].item(), trav_launches=t[3].item(), launches=sm[4].item(), build_ms=mx[5].item() / steps, steps_ms=ms)
+        return dict(ms=total_ms, rays=float(rays), trav_ms=trav_ms, trav_launches=float(trav_launches), launches=float(launches), build_ms=sum(bms) / steps, steps_ms=ms)
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    dev_res = timed(step_device, a.steps, a.warmup)
-    sampler.stop_flag = True
+    dev_res = timed(step_device, a.steps, a.warmup, sampler)
     e2e_res = timed(step_host, a.steps, max(1, a.warmup - 1))
     ser_res = timed(step_device_serial, a.steps, 1)  # same frames, one pass at a time, traverse launches timed
 
@@ -413,6 +422,8 @@ def run_b200(a):
         "config": {"workload": workload_name(a), "lane": "near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)",
                    "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
                    "parallelism": "scene replicated, image in interleaved %dx%d tiles over %d GPU(s), NCCL broadcast + framebuffer reduce; two passes in flight per GPU" % (parallel.tile_shape(world, W) + (world,))},
+        "ms_steps_rank0": {"device": [round(x, 3) for x in dev_res["steps_ms"]], "e2e": [round(x, 3) for x in e2e_res["steps_ms"]],
+                           "serial_passes": [round(x, 3) for x in ser_res["steps_ms"]]},  # this rank's own event time of every timed step
         "ms_per_step_serial_passes": ser_res["ms"] / a.steps,
         "lbvh_build_ms": dev_res["build_ms"],  # inside the timed frames (asynchronous, read back after each frame)
         "lbvh_build_ms_alone": build_alone,   # best of 3 with an idle GPU and a synchronising call
@@ -430,7 +441,7 @@ def run_b200(a):
                      "timed_how": "CUDA events around every traverse launch of %d frames rendered one pass at a time (RT_RENDER_SERIAL_PASSES), %.2f ms per frame; the headline frames keep two passes in flight, where a launch interval would include waiting for the other pass" % (a.steps, ser_res["ms"] / a.steps),
                      "l2_gather_peak": l2.get("l2_gather64_gbs"), "frac_of_l2_gather": (achieved / l2["l2_gather64_gbs"]) if l2.get("l2_gather64_gbs") else None,
                      "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test. The 64 MB of nodes and 96 MB of leaf records are served by L2 (92-96 % hit rate, DRAM traffic = rays in + hits out), so the rate can exceed the HBM copy peak; the bound that applies is the measured L2 rate for 64-byte random gathers (profiles/l2_peaks_r01.json, BASELINE.json's 'traversal roofline ... against L2 bandwidth')"},
-        "clocks": sampler.summary(),
+        "clocks": sampler.summary() if sampler is not None else None,
     }
     if diag:
         line["scaling_diag"] = diag

@@ -362,9 +362,15 @@ __device__ __forceinline__ V3 rough_offset(float rough, Xorwow& rng, int zyx) {
 // (T_W_PRIMARY, bounces, weight 1) and whose accumulator is zero, so neither is stored by generate nor loaded here.
 template <bool FULL, bool FIRST>
 __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
-                                                   const float4* __restrict__ qin, const unsigned n_front, const unsigned n_back,
-                                                   float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
-  const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+                                                   const float4* __restrict__ qin, const unsigned n_front_in, const unsigned n_back_in,
+                                                   float4* __restrict__ qout, int32_t* __restrict__ hit_id_out,
+                                                   const unsigned* __restrict__ counts_dev) {
+  // counts_dev != nullptr: a pass queued without host round trips — the ray counts are read here, the grid is an upper
+  // bound (or smaller: the blocks stride over the queue), B.counters is the NEXT iteration's counter block
+  const unsigned n_front = counts_dev ? counts_dev[1] : n_front_in, n_back = counts_dev ? counts_dev[5] : n_back_in;
+  __shared__ unsigned s_app[2 * 4 + 2];
+  for (unsigned g0 = blockIdx.x * blockDim.x; g0 < n_front + n_back; g0 += gridDim.x * blockDim.x) {  // block-uniform
+  const unsigned g = g0 + threadIdx.x;
   bool emit = false, shaded = false; V3 eo = mk3(0, 0, 0), ed = mk3(0, 0, 0); float elimit = INFINITY; unsigned etag = 0u;
   if (g < n_front + n_back) {
     const unsigned r = g < n_front ? g : (unsigned)P.S - n_back + (g - n_front);  // queue slot: front end, then back end
@@ -616,10 +622,10 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
 #undef NEED_RNG
 #undef NEED_ACC
   }
-  __shared__ unsigned s_app[2 * 4 + 2];
   queue_append_block<4>(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, emit, eo, ed, elimit, etag, s_app);
   const int nshaded = __syncthreads_count(shaded);  // one atomic per block: a single hot counter serialises in L2
   if (nshaded && threadIdx.x == 0) atomicAdd(B.stats + 2, (unsigned long long)nshaded);
+  }
 }
 
 // ---- resolve: sample sum in the butterfly order of render_kernel_warp_aa, sRGB, 8-bit store -----
@@ -727,6 +733,8 @@ struct RenderState {
   RngTables rng;
   cudaEvent_t e0 = nullptr, e1 = nullptr, t0[2] = {nullptr, nullptr}, t1[2] = {nullptr, nullptr}, ev_cnt[2] = {nullptr, nullptr};
   cudaStream_t pass_stream = nullptr; cudaEvent_t ev_fork2 = nullptr, ev_join2 = nullptr;  // second pass in flight
+  uint32_t* h_blocks = nullptr; size_t h_blocks_words = 0;  // pinned: counter blocks of every queued pass of a frame
+  std::vector<cudaEvent_t> ev_pool;                         // traverse timing of queued passes
   cudaStream_t head_stream = nullptr; cudaEvent_t ev_join = nullptr;  // RT_RENDER_OVERLAP_BUILD
   int trav_grid = 0;
   uint8_t* d_rgba = nullptr; int32_t* d_ids = nullptr; uint8_t* d_written = nullptr; size_t img_px = 0;  // rt_render_host staging
@@ -740,7 +748,7 @@ RenderState* get_state(rt_scene* s) {
 
 int ensure_common(rt_scene* s, RenderState* st) {
   if (!st->counters) {
-    RT_CUDA(cudaMalloc(&st->counters, 128));
+    RT_CUDA(cudaMalloc(&st->counters, 2 * 256 * 4));  // 2 pass contexts x 16 blocks x 16 words
     RT_CUDA(cudaMalloc(&st->stats, 128));
     RT_CUDA(cudaMallocHost(&st->h_count, 128));
     RT_CUDA(cudaEventCreate(&st->e0)); RT_CUDA(cudaEventCreate(&st->e1));
@@ -774,34 +782,39 @@ int lane_of(unsigned flags) {
 // ctr: [0] fetch ticket front, [3] fallback count, [4] fallback fetch ticket, [6] fetch ticket back.
 template <bool EXACT>
 void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
-                 float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count) {
+                 float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
   if (sun) {
-    if (count) traverse_near_kernel<EXACT, true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
-    else traverse_near_kernel<EXACT, false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
+    if (count) traverse_near_kernel<EXACT, true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_near_kernel<EXACT, false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
   } else {
-    if (count) traverse_near_kernel<EXACT, true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
-    else traverse_near_kernel<EXACT, false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count);
+    if (count) traverse_near_kernel<EXACT, true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_near_kernel<EXACT, false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
   }
 }
+// counts_dev == nullptr: nf / nb are the ray counts (the host read them back).  counts_dev != nullptr (a pass queued without host
+// round trips): the kernels read the counts from counts_dev[1] (front) and counts_dev[5] (back); nf / nb only say which
+// ends can hold rays at all (0 = skip the launch), and the grids are the full persistent grid.
 int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned nf, unsigned nb,
-                    unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list) {
+                    unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list, const unsigned* counts_dev = nullptr) {
   int launches = 0;
   for (int end = 0; end < 2; end++) {
     const unsigned n = end ? nb : nf, first = end ? cap - nb : 0u;
     if (n == 0) continue;
     unsigned* fetch = ctr + (end ? 6 : 0);
-    const int grid = (int)std::min<long long>(max_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
+    const unsigned* n_dev = counts_dev ? counts_dev + (end ? 5 : 1) : nullptr;
+    const unsigned cap_back = (counts_dev && end) ? cap : 0u;
+    const int grid = counts_dev ? max_grid : (int)std::min<long long>(max_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
     if (lane == RT_LANE_REF) {
-      if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr);
-      else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr);
-    } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3);
-    else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3);
+      if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
+      else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
+    } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
+    else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
     launches++;
   }
   if (lane == RT_LANE_EXACT && nf + nb > 0) {
     const int g2 = max_grid < 148 ? max_grid : 148;
-    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3);
-    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3);
+    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u);
+    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u);
     launches++;
   }
   return launches;
@@ -850,6 +863,8 @@ int rt_render_free_state(rt_scene* s) {
     cudaEventDestroy(st->e0); cudaEventDestroy(st->e1);
     for (int k = 0; k < 2; k++) { cudaEventDestroy(st->t0[k]); cudaEventDestroy(st->t1[k]); cudaEventDestroy(st->ev_cnt[k]); }
   }
+  if (st->h_blocks) cudaFreeHost(st->h_blocks);
+  for (cudaEvent_t e : st->ev_pool) cudaEventDestroy(e);
   if (st->pass_stream) { cudaStreamDestroy(st->pass_stream); cudaEventDestroy(st->ev_fork2); cudaEventDestroy(st->ev_join2); }
   if (st->head_stream) { cudaStreamDestroy(st->head_stream); cudaEventDestroy(st->ev_join); }
   delete st;
@@ -918,7 +933,12 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
 
   // pass size: all per-sample state of a pass lives in one pool (RT_POOL_BYTES each, default 6 GB)
   const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8 + 4;
-  const size_t budget = env_size("RT_POOL_BYTES", (size_t)6 << 30);
+  // 16 GB per pool (two pools): the 4K x 16 spp frame is two passes = 4 traverse launches instead of 12 with 6 GB pools,
+  // and every launch costs ~0.46 ms whatever its size (measured 47.6 -> 46.6 ms per frame).  A B200 has 180 GB; on a
+  // smaller or busy device the default shrinks to a quarter of the free memory.
+  size_t dflt_pool = (size_t)16 << 30;
+  { size_t fr = 0, tot = 0; if (cudaMemGetInfo(&fr, &tot) == cudaSuccess) { size_t have = fr; for (int k = 0; k < 2; k++) have += rs->pool_bytes[k]; dflt_pool = std::min(dflt_pool, std::max<size_t>(have / 4, (size_t)64 << 20)); } }
+  const size_t budget = env_size("RT_POOL_BYTES", dflt_pool);
   const long long total_samples = nslots * P.spp;
   long long max_s = (long long)(budget / per_sample);
   long long npix_pass = std::max<long long>(1, max_s / P.spp);
@@ -929,14 +949,16 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   // 25 M rays is ~30x the mean, so the last ~0.4 ms of a launch keep a handful of warps busy on an otherwise empty
   // GPU.  Passes are independent (disjoint pixels), so two of them run on two streams with a pool each: while one
   // pass drains, the CTAs of the other pass's kernels fill the SMs it leaves.  The host alternates between the two
-  // (it blocks on one pass's ray counts while the other pass's kernels are queued), so neither stream runs dry.  A
-  // frame that fits one pass is split in two for the same reason.  Same pixels: a pass is the same computation on
+  // (it blocks on one pass's ray counts while the other pass's kernels are queued), so neither stream runs dry.
+  // Same pixels: a pass is the same computation on
   // whichever stream it runs (tests/test_render_gpu.py::test_multi_pass_equals_single_pass and the parity suite).
   const bool serial = (flags & RT_RENDER_SERIAL_PASSES) != 0 || getenv("RT_SERIAL_PASSES") != nullptr;
-  const int nctx = (!serial && total_samples >= (1ll << 21)) ? 2 : 1;
+  // A frame that fits one pass stays one pass: splitting it in two hides one drain and pays two more launches
+  // (measured: 24.2 ms as one pass, 25.0 ms as two half passes in flight on a 1/2 slice of the 4K frame).
+  const long long npass0 = nslots > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
+  const int nctx = (!serial && npass0 >= 2) ? 2 : 1;
   if (nslots > 0) {  // balanced passes (an even number of them when two are in flight)
-    long long npass = (nslots + npix_pass - 1) / npix_pass;
-    if (nctx == 2) npass = (npass + 1) & ~1ll;
+    const long long npass = nctx == 2 ? ((npass0 + 1) & ~1ll) : npass0;
     npix_pass = std::min<long long>(nslots, std::max<long long>(32, ((nslots + npass - 1) / npass + 31) & ~31ll));
   } else npix_pass = 0;
   const size_t Smax = (size_t)npix_pass * P.spp;
@@ -970,7 +992,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     B.qa = (float4*)p; p += al(Smax * 32); B.qb = (float4*)p; p += al(Smax * 32);
     B.hits = (float2*)p; p += al(Smax * 8);
     B.fb_list = (unsigned*)p; p += al(Smax * 4);
-    c.counters = rs->counters + 16 * k; c.h_count = rs->h_count + 16 * k;
+    c.counters = rs->counters + 256 * k; c.h_count = rs->h_count + 16 * k;  // 16 counter blocks of 16 words per context
     B.counters = c.counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
     c.st = k == 0 ? st : rs->pass_stream;
     c.ev_cnt = rs->ev_cnt[k]; c.t0 = rs->t0[k]; c.t1 = rs->t1[k];
@@ -995,7 +1017,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (d_written) RT_CUDA(cudaMemsetAsync(d_written, 0, (size_t)npx, hs));
   if (d_hit_id) RT_CUDA(cudaMemsetAsync(d_hit_id, 0xFF, (size_t)npx * 4, hs));
   RT_CUDA(cudaMemsetAsync(rs->stats, 0, 128, hs));
-  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 128, hs));
+  RT_CUDA(cudaMemsetAsync(rs->counters, 0, 2 * 256 * 4, hs));
   if (nctx == 2) {  // the second pass stream starts after the caller's work on `st` (the build) and after the clears
     RT_CUDA(cudaEventRecord(rs->ev_fork2, st));
     RT_CUDA(cudaStreamWaitEvent(rs->pass_stream, rs->ev_fork2, 0));
@@ -1060,10 +1082,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       {
         const unsigned sg = (n_front + n_back + 127) / 128;
         const bool first = c.iter_in_pass == 0;
-        if (P.full_shade) { if (first) shade_kernel<true, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id);
-                            else shade_kernel<true, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id); }
-        else { if (first) shade_kernel<false, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id);
-               else shade_kernel<false, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id); }
+        if (P.full_shade) { if (first) shade_kernel<true, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id, nullptr);
+                            else shade_kernel<true, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id, nullptr); }
+        else { if (first) shade_kernel<false, true><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id, nullptr);
+               else shade_kernel<false, false><<<sg, 128, 0, c.st>>>(c.P, sc, c.B, c.qin, n_front, n_back, c.qout, d_hit_id, nullptr); }
         c.iter_in_pass++;
       }
       launches++;
@@ -1079,10 +1101,76 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     if (next_slot0 < nslots) return start_pass(c);
     return RT_OK;
   };
-  for (int k = 0; k < nctx && err == RT_OK && next_slot0 < nslots; k++) err = start_pass(ctx[k]);
-  while (err == RT_OK && (ctx[0].active || ctx[1].active))
-    for (int k = 0; k < nctx && err == RT_OK; k++)
-      if (ctx[k].active) err = advance(ctx[k]);
+  // QUEUED PASSES.  Without mirrors, glass or GI a sample's life is: primary ray, then one shadow ray per light, so a
+  // pass is exactly 1 + num_lights wavefront iterations and nothing about its launches depends on the ray counts
+  // except sizes.  The kernels then read their ray counts from device memory (one counter block per iteration:
+  // generate fills block 0, iteration k traverses the counts of block k and its shade kernel appends to block k+1),
+  // the whole frame is queued without a single host round trip, and the counts come back in one copy per pass for
+  // the accounting.  No bubbles between kernels, and nothing for a busy host to delay.  Scenes whose continuation
+  // stack can hold pending calls keep the host-driven loop above (their iteration count depends on the data).
+  const int nl = P.num_lights;
+  const bool queued = !P.full_shade && nl + 2 <= 16 && getenv("RT_HOST_DRIVEN") == nullptr;
+  const long long npasses_total = npix_pass > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
+  if (queued && npasses_total > 0) {
+    const size_t words = (size_t)npasses_total * 256;
+    if (words > rs->h_blocks_words) {
+      if (rs->h_blocks) cudaFreeHost(rs->h_blocks);
+      rs->h_blocks = nullptr; rs->h_blocks_words = 0;
+      RT_CUDA(cudaMallocHost(&rs->h_blocks, words * 4));
+      rs->h_blocks_words = words;
+    }
+    const size_t nev = time_trav ? (size_t)npasses_total * (nl + 1) * 2 : 0;
+    while (rs->ev_pool.size() < nev) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); rs->ev_pool.push_back(e); }
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+    for (long long pi = 0; pi < npasses_total; pi++) {
+      PassCtx& c = ctx[pi % nctx];
+      c.P = P;
+      c.P.slot0 = (int)next_slot0; c.P.npix = (int)std::min<long long>(npix_pass, nslots - next_slot0); c.P.S = c.P.npix * c.P.spp;
+      next_slot0 += npix_pass;
+      passes++; samples += (uint64_t)c.P.S;
+      cudaStream_t gs = (!head_joined && c.st == st) ? hs : c.st;
+      RT_CUDA(cudaMemsetAsync(c.counters, 0, (size_t)(nl + 2) * 64, gs));
+      if (c.P.mode != 2 && c.P.need_rng) {
+        const int hn = (int)(((npx + 255) / 256 + 31) & ~31ll);
+        rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, gs>>>(c.P, c.B, hn);
+        launches++;
+      }
+      generate_kernel<<<(unsigned)((c.P.S + 256 * RT_GEN_CHUNKS - 1) / (256 * RT_GEN_CHUNKS)), 256, 0, gs>>>(c.P, c.B, c.B.qa, d_hit_id);  // counts -> block 0
+      launches++;
+      RT_CUDA(cudaGetLastError());
+      if (gs != c.st) {
+        RT_CUDA(cudaEventRecord(rs->ev_join, gs));
+        RT_CUDA(cudaStreamWaitEvent(c.st, rs->ev_join, 0));
+        head_joined = true;
+      }
+      float4 *qin = c.B.qa, *qout = c.B.qb;
+      const unsigned sgrid = (unsigned)std::min<long long>(((long long)c.P.S + 127) / 128, (long long)sms * RT_SHADE_MIN_CTAS * 4);
+      for (int it = 0; it <= nl; it++) {
+        uint32_t* blk = c.counters + 16 * it;
+        // which queue ends can hold rays: primary rays go to the front; shadow rays to a sun go to the back, to a bulb to the front
+        const unsigned may_front = it == 0 ? 1u : (s->cfg.num_bulbs > 0 ? 1u : 0u), may_back = it == 0 ? 0u : (s->cfg.num_suns > 0 ? 1u : 0u);
+        if (time_trav) RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + it)], c.st));
+        const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, c.st, sc, (const float4*)qin, may_front, may_back, (unsigned)c.P.S, c.B.hits,
+                                       blk, rs->stats, c.B.fb_list, blk);
+        launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);
+        if (time_trav) RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + it) + 1], c.st));
+        RenderBuffers Bn = c.B; Bn.counters = blk + 16;  // this iteration's shade appends the next iteration's rays
+        if (it == 0) shade_kernel<false, true><<<sgrid, 128, 0, c.st>>>(c.P, sc, Bn, qin, 0u, 0u, qout, d_hit_id, blk);
+        else shade_kernel<false, false><<<sgrid, 128, 0, c.st>>>(c.P, sc, Bn, qin, 0u, 0u, qout, d_hit_id, blk);
+        launches++;
+        std::swap(qin, qout);
+      }
+      resolve_kernel<<<(c.P.npix + 127) / 128, 128, 0, c.st>>>(c.P, c.B, d_rgba, d_written);
+      launches++;
+      RT_CUDA(cudaGetLastError());
+      RT_CUDA(cudaMemcpyAsync(rs->h_blocks + 256 * pi, c.counters, (size_t)(nl + 2) * 64, cudaMemcpyDeviceToHost, c.st));
+    }
+  } else {
+    for (int k = 0; k < nctx && err == RT_OK && next_slot0 < nslots; k++) err = start_pass(ctx[k]);
+    while (err == RT_OK && (ctx[0].active || ctx[1].active))
+      for (int k = 0; k < nctx && err == RT_OK; k++)
+        if (ctx[k].active) err = advance(ctx[k]);
+  }
 #undef RT_PASS_CUDA
   if (err != RT_OK) { const std::string keep = rt_last_error(); cudaDeviceSynchronize(); rt_set_error(keep); return err; }  // nothing of this frame stays in flight
   if (!head_joined) {  // nothing to render: the clears still belong to this call
@@ -1095,6 +1183,19 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   }
   RT_CUDA(cudaEventRecord(rs->e1, st));
   RT_CUDA(cudaEventSynchronize(rs->e1));
+  if (queued) {  // the accounting of the queued passes, from their counter blocks
+    bool overflow = false;
+    for (long long pi = 0; pi < npasses_total; pi++)
+      for (int it = 0; it <= nl; it++) {
+        const uint32_t* blk = rs->h_blocks + 256 * pi + 16 * it;
+        const uint64_t nr = (uint64_t)blk[1] + blk[5];
+        if (nr) iters++;
+        rays += nr; fb_rays += blk[3];
+        overflow = overflow || blk[16 + 2] != 0u;
+        if (time_trav) { float ms = 0.f; RT_CUDA(cudaEventElapsedTime(&ms, rs->ev_pool[2 * (pi * (nl + 1) + it)], rs->ev_pool[2 * (pi * (nl + 1) + it) + 1])); trav_ms += ms; }
+      }
+    if (overflow) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
+  }
   if (counters) {
     memset(counters, 0, sizeof(*counters));
     counters->rays = rays; counters->samples = samples; counters->wavefront_iters = iters; counters->passes = passes;

@@ -274,10 +274,14 @@ __device__ __forceinline__ RtHit rt_trace_ref(const RtDeviceScene& sc, const V3 
 // list == nullptr: the n rays of the queue from slot `first`, 32 at a time per warp.  list != nullptr: the rays whose indices the
 // near-first kernel appended (their hits are written here).
 template <bool COUNT>
-__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
-                                                                      const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
+__global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
+                                                                      const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                       unsigned long long* stats, const unsigned* __restrict__ list,
-                                                                      const unsigned* __restrict__ list_count) {
+                                                                      const unsigned* __restrict__ list_count,
+                                                                      const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+  // n_dev != nullptr: the ray count is read on the device (a pass queued without host round trips, render.cu);
+  // cap_back != 0: the rays are the back end of the queue, slots [cap_back - n, cap_back)
+  const unsigned n = n_dev ? *n_dev : n_in, first = (n_dev && cap_back) ? cap_back - n : first_in;
   __shared__ unsigned s_ref[RT_STACK_SHARED][RT_TRAV_THREADS];
   RtStack S; S.ref = s_ref; S.key = nullptr;
   const unsigned lane = threadIdx.x & 31;
@@ -326,10 +330,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 #define RT_TRAV_MIN_CTAS 1
 #endif
 template <bool EXACT, bool COUNT, bool SUN>
-__global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first,
-                                                                       const unsigned n, float2* __restrict__ hits, unsigned* fetch_counter,
+__global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
+                                                                       const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
-                                                                       unsigned* fb_count) {
+                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+  const unsigned n = n_dev ? *n_dev : n_in, first = (n_dev && cap_back) ? cap_back - n : first_in;  // see traverse_ref_kernel
   // stack entry = (reference, culling key): one 64-bit shared-memory access per push / pop (SUN: references only)
   __shared__ unsigned s_ref[SUN ? RT_STACK_SHARED : 1][RT_TRAV_THREADS];
   __shared__ uint2 s_ent[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];

@@ -411,3 +411,37 @@ def test_frame_loop_overlapped_head_gives_the_same_pixels():
         a0, a1 = out[(0, f)], out[(api.RENDER_OVERLAP_BUILD, f)]
         assert np.array_equal(a0[0], a1[0]) and np.array_equal(a0[1], a1[1]) and a0[2] == a1[2]
     assert not np.array_equal(out[(0, 0)][0], out[(0, 2)][0])  # the frames do differ
+
+
+def test_pass_schedules_give_the_same_pixels(monkeypatch):
+    """rt_render has three ways to run the passes of a frame: queued without host round trips (scenes without mirrors,
+    glass or GI: the kernels read their ray counts on the device), host-driven with two passes in flight, and
+    host-driven one pass at a time (RT_RENDER_SERIAL_PASSES).  Same bytes, ids and ray counts, with one pass and with
+    many, for a sun + bulb scene (both queue ends in use) and for the soup."""
+    cases = []
+    cfg, a = synth.soup(50_000, seed=3, width=320, height=200, aa=4)
+    a = synth.finish_triangles(a)
+    cases.append(H.oracle_from_arrays(cfg, a))
+    o2 = H.oracle_from_arrays(cfg, a); o2.add_bulb((0.5, 0.8, 2.5), (3, 3, 3)); o2.add_sun((-1, 2, 1), (0.5, 0.4, 0.3))
+    cases.append(o2)
+    for o in cases:
+        ref = None
+        for pool in (None, 2_000_000):
+            for host_driven in (False, True):
+                for flags in (api.SPP_TRUE, api.SPP_TRUE | api.RENDER_SERIAL_PASSES):
+                    if pool is None: monkeypatch.delenv("RT_POOL_BYTES", raising=False)
+                    else: monkeypatch.setenv("RT_POOL_BYTES", str(pool))
+                    if host_driven: monkeypatch.setenv("RT_HOST_DRIVEN", "1")
+                    else: monkeypatch.delenv("RT_HOST_DRIVEN", raising=False)
+                    sc = built_pair(o)
+                    r = sc.render(320, 200, 4, flags, want_ids=True, want_written=True)
+                    sc.close()
+                    if pool is not None:
+                        assert r["counters"].passes >= 4
+                    if ref is None:
+                        ref = r
+                        assert (r["ids"] >= 0).mean() > 0.05 and r["counters"].rays > 320 * 200 * 4
+                        continue
+                    assert np.array_equal(r["rgba"], ref["rgba"]) and np.array_equal(r["ids"], ref["ids"]) and np.array_equal(r["written"], ref["written"])
+                    assert r["counters"].rays == ref["counters"].rays and r["counters"].samples == ref["counters"].samples
+                    assert r["counters"].wavefront_iters >= ref["counters"].wavefront_iters - 0  # queued passes count non-empty iterations like the host loop
