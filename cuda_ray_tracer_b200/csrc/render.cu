@@ -955,7 +955,8 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   const bool serial = (flags & RT_RENDER_SERIAL_PASSES) != 0 || getenv("RT_SERIAL_PASSES") != nullptr;
   // A frame that fits one pass stays one pass: splitting it in two hides one drain and pays two more launches
   // (measured: 24.2 ms as one pass, 25.0 ms as two half passes in flight on a 1/2 slice of the 4K frame).
-  const long long npass0 = nslots > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
+  long long npass0 = nslots > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
+  if (const char* e = getenv("RT_MIN_PASSES")) { const long long v = atoll(e); if (npass0 > 0 && v > npass0 && total_samples >= (1ll << 21)) npass0 = v; }  // experiments
   const int nctx = (!serial && npass0 >= 2) ? 2 : 1;
   if (nslots > 0) {  // balanced passes (an even number of them when two are in flight)
     const long long npass = nctx == 2 ? ((npass0 + 1) & ~1ll) : npass0;
