@@ -440,7 +440,8 @@ def run_b200(a):
                      "share_of_step": ser_res["trav_ms"] / ser_res["ms"],
                      "timed_how": "CUDA events around every traverse launch of %d frames rendered one pass at a time (RT_RENDER_SERIAL_PASSES), %.2f ms per frame; the headline frames keep two passes in flight, where a launch interval would include waiting for the other pass" % (a.steps, ser_res["ms"] / a.steps),
                      "l2_gather_peak": l2.get("l2_gather64_gbs"), "frac_of_l2_gather": (achieved / l2["l2_gather64_gbs"]) if l2.get("l2_gather64_gbs") else None,
-                     "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test. The 64 MB of nodes and 96 MB of leaf records are served by L2 (92-96 % hit rate, DRAM traffic = rays in + hits out), so the rate can exceed the HBM copy peak; the bound that applies is the measured L2 rate for 64-byte random gathers (profiles/l2_peaks_r01.json, BASELINE.json's 'traversal roofline ... against L2 bandwidth')"},
+                     "l2_gather_pair_peak": l2.get("l2_gather64_pair_shfl_gbs"), "frac_of_l2_gather_pair": (achieved / l2["l2_gather64_pair_shfl_gbs"]) if l2.get("l2_gather64_pair_shfl_gbs") else None,
+                     "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test. The 64 MB of nodes and 96 MB of leaf records are served by L2 (92-96 % hit rate, DRAM traffic = rays in + hits out), so the rate can exceed the HBM copy peak; the bound that applies is the measured L2 rate for 64-byte random gathers (profiles/l2_peaks_r01.json, BASELINE.json's 'traversal roofline ... against L2 bandwidth'): l2_gather_peak with one load per lane (what the kernel does), l2_gather_pair_peak when lane pairs share each record's 128-byte line (half the L1TEX wavefronts; the same fetch inside the kernel lost 18-25 % to its shuffles and registers, DESIGN.md 4.2)"},
         "clocks": sampler.summary() if sampler is not None else None,
     }
     if diag:
