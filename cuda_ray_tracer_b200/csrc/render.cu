@@ -728,6 +728,7 @@ struct RngTables {  // device copies of the skip-ahead matrices, one set per dev
 
 struct RenderState {
   char* pool[2] = {nullptr, nullptr}; size_t pool_bytes[2] = {0, 0};  // one per pass in flight
+  size_t dflt_pool = 0;  // default RT_POOL_BYTES of this device
   uint32_t* counters = nullptr; unsigned long long* stats = nullptr;  // counters: 16 words per pass context
   uint32_t* h_count = nullptr;  // pinned, 16 words per pass context
   RngTables rng;
@@ -936,9 +937,12 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   // 16 GB per pool (two pools): the 4K x 16 spp frame is two passes = 4 traverse launches instead of 12 with 6 GB pools,
   // and every launch costs ~0.46 ms whatever its size (measured 47.6 -> 46.6 ms per frame).  A B200 has 180 GB; on a
   // smaller or busy device the default shrinks to a quarter of the free memory.
-  size_t dflt_pool = (size_t)16 << 30;
-  { size_t fr = 0, tot = 0; if (cudaMemGetInfo(&fr, &tot) == cudaSuccess) { size_t have = fr; for (int k = 0; k < 2; k++) have += rs->pool_bytes[k]; dflt_pool = std::min(dflt_pool, std::max<size_t>(have / 4, (size_t)64 << 20)); } }
-  const size_t budget = env_size("RT_POOL_BYTES", dflt_pool);
+  if (rs->dflt_pool == 0) {  // decided once per scene (cudaMemGetInfo is a driver round trip, not something for every frame)
+    rs->dflt_pool = (size_t)16 << 30;
+    size_t fr = 0, tot = 0;
+    if (cudaMemGetInfo(&fr, &tot) == cudaSuccess) rs->dflt_pool = std::min(rs->dflt_pool, std::max<size_t>(fr / 4, (size_t)64 << 20));
+  }
+  const size_t budget = env_size("RT_POOL_BYTES", rs->dflt_pool);
   const long long total_samples = nslots * P.spp;
   long long max_s = (long long)(budget / per_sample);
   long long npix_pass = std::max<long long>(1, max_s / P.spp);

@@ -1,5 +1,5 @@
 #!/bin/bash
-# end-of-round GPU call: full GPU suite, smoke, default bench (+ reference arm), config-5-size bench, ncu launch list and
+# one GPU call that checks a round (usage: gpurun --timeout 2400 -- bash scripts/gpu_round_check.sh): full GPU suite, smoke, default bench (+ reference arm), config-5-size bench, ncu launch list and
 # one --set full capture of the traversal kernel of the bench command
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm --format=csv,noheader > gpurun_out/gpu.txt
