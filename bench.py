@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--near-first", action="store_true", help="RT_TRAVERSE_NEAR_FIRST lane (not bit-exact in rare cases)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--overlap-build", action="store_true", help="device leg: RT_RENDER_OVERLAP_BUILD (the frame's ray generation runs beside update+build), as the e2e leg always does")
+    ap.add_argument("--wide4", action="store_true", help="EXPERIMENTAL: RT_BUILD_WIDE4, the near-first lanes step through a 4-wide tree of grandchildren")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true", help="skip timing the reference's own CUDA build (oracle/_ref/ref_gpu_fast) on this GPU")
     return ap.parse_args()
@@ -291,12 +292,14 @@ def run_b200(a):
     # device leg it gains nothing (generation already fills the GPU, the build just stretches), so that leg keeps the
     # plain stream order and its lbvh_build_ms is the build running alone.
     rflags_e2e = rflags | api.RENDER_OVERLAP_BUILD
-    BUILD_LAUNCHES = 1 + 8  # update_tris + init, bounds, morton, 4 onesweep passes, bottom-up
+    BUILD_LAUNCHES = 1 + 8 + (1 if a.wide4 else 0)  # update_tris + init, bounds, morton, 4 onesweep passes, bottom-up (+ collapse)
+    bflags = api.BOUNDS_COMPUTED | (api.BUILD_WIDE4 if a.wide4 else 0)
+    node_bytes = 128.0 if a.wide4 else 64.0  # bytes of one node step
 
     def step_device(f, cnt, flags=None):
         fr = frames_d[f % nframes]
         sc.update_triangles(fr[0], fr[1], fr[2])
-        sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED, timed=False)  # asynchronous: its device time is read after the frame
+        sc.build_lbvh_karas(30, bflags, timed=False)  # asynchronous: its device time is read after the frame
         sc.render_device(W, Hh, spp, img_d, flags=rflags if flags is None else flags, tiles=tiles, counters=cnt)
         parallel.gather_framebuffer(img_d, 0)  # tiles are disjoint and the rest is zero: sum == gather
         return sc.build_ms()
@@ -317,7 +320,7 @@ def run_b200(a):
             sc.update_triangles(full[0], full[1], full[2])
         else:
             sc.update_triangles(fr[0], fr[1], fr[2])   # host pointers: H2D inside
-        sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED, timed=False)
+        sc.build_lbvh_karas(30, bflags, timed=False)
         if world > 1:
             sc.render_device(W, Hh, spp, img_d, flags=rflags_e2e, tiles=tiles, counters=cnt)
             parallel.gather_framebuffer(img_d, 0)
@@ -366,10 +369,10 @@ def run_b200(a):
     cnt = api.Counters()
     fr = frames_d[a.warmup % nframes]
     sc.update_triangles(fr[0], fr[1], fr[2]); torch.cuda.synchronize()
-    build_alone = min(sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED) for _ in range(3))  # nothing else on the GPU
+    build_alone = min(sc.build_lbvh_karas(30, bflags) for _ in range(3))  # nothing else on the GPU
     sc.render_device(W, Hh, spp, img_d, flags=(rflags & ~api.TIME_TRAVERSE) | api.COUNTERS, tiles=tiles, counters=cnt)
     torch.cuda.synchronize()
-    alg = torch.tensor([64.0 * cnt.nodes_visited + 48.0 * cnt.leaf_tests, float(cnt.nodes_visited), float(cnt.leaf_tests), float(cnt.rays)],
+    alg = torch.tensor([node_bytes * cnt.nodes_visited + 48.0 * cnt.leaf_tests, float(cnt.nodes_visited), float(cnt.leaf_tests), float(cnt.rays)],
                        dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(alg, op=dist.ReduceOp.SUM)
@@ -419,7 +422,7 @@ def run_b200(a):
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": dev_res["ms"] / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(a), "lane": "near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)",
+        "config": {"workload": workload_name(a), "lane": ("near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)") + (", 4-wide tree (experimental)" if a.wide4 else ""),
                    "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
                    "parallelism": "scene replicated, image in interleaved %dx%d tiles over %d GPU(s), NCCL broadcast + framebuffer reduce; two passes in flight per GPU" % (parallel.tile_shape(world, W) + (world,))},
         "ms_steps_rank0": {"device": [round(x, 3) for x in dev_res["steps_ms"]], "e2e": [round(x, 3) for x in e2e_res["steps_ms"]],

@@ -314,6 +314,33 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   }
 }
 
+// ---- 4-wide tree over the same leaves (RT_BUILD_WIDE4, experimental) ---------------------------------------
+// Wide node i (same slot as binary node i) holds up to four 32-byte halves: for each child of node i, the child's own
+// half if it is a leaf, else the two halves of the child node.  Unused places hold NaN boxes (never hit).  One thread
+// per slot; a slot that no wide step can reach (odd depth) is built as well, it costs nothing to have.
+__global__ void __launch_bounds__(256) collapse4_kernel(const float4* __restrict__ nodes, int n, float4* __restrict__ wnodes) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  const float nan = __int_as_float(0x7fc00000);
+  float4 out[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) out[k] = make_float4(nan, nan, nan, nan);
+  int c = 0;
+  for (int side = 0; side < 2; side++) {
+    const float4 h0 = nodes[4 * (size_t)i + 2 * side], h1 = nodes[4 * (size_t)i + 2 * side + 1];
+    const uint32_t ref = __float_as_uint(h1.z);
+    if (ref & RT_LEAF_BIT) { out[2 * c] = h0; out[2 * c + 1] = h1; c++; }
+    else {
+      const float4* g = nodes + 4 * (size_t)ref;
+      out[2 * c] = g[0]; out[2 * c + 1] = g[1]; c++;
+      out[2 * c] = g[2]; out[2 * c + 1] = g[3]; c++;
+    }
+  }
+  for (int k = 2 * c; k < 8; k++) out[k].z = (k & 1) ? __uint_as_float(0u) : nan;  // ref word of an unused place
+#pragma unroll
+  for (int k = 0; k < 8; k++) wnodes[8 * (size_t)i + k] = out[k];
+}
+
 // ---- export in the reference's layouts --------------------------------------------------------
 struct RefNode44 {  // include/lbvh.cuh:6-28
   float bbox[6]; uint32_t left, right, prim; uint16_t nleaf; uint16_t pad; uint32_t counter;
@@ -391,6 +418,11 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
       bottom_up_local_kernel<uint32_t><<<gl, RT_BU_CHUNK, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
     else
       bottom_up_local_kernel<uint64_t><<<gl, RT_BU_CHUNK, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+  }
+  s->built_wide = false;
+  if ((flags & RT_BUILD_WIDE4) && n > 1) {
+    collapse4_kernel<<<(n - 1 + 255) / 256, 256, 0, st>>>(s->nodes, n, s->wnodes);
+    s->built_wide = true;
   }
   RT_CUDA(cudaGetLastError());
   s->built = true; s->built_bits = morton_bits; s->built_topdown = (flags & RT_BUILD_TOPDOWN) != 0;

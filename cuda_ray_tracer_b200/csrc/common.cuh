@@ -60,6 +60,7 @@ struct RtDeviceScene {  // device pointers, passed to kernels by value
   int n;                // primitives
   const int* root;      // device word holding the root node slot (or leaf ref if n == 1): read by the kernels, never by the host
   const float4* nodes;
+  const float4* wnodes;  // 4-wide nodes (RT_BUILD_WIDE4) or nullptr: 128 bytes = the four grandchildren's halves, same slot numbering
   const float4* sorted_tv;
   const uint32_t* perm;  // sorted position -> file-order index
   const float4* prim_mat;
@@ -75,7 +76,7 @@ struct rt_scene {
   bool any_shiny = false, any_trans = false, any_rough = false;
   // arena
   char* arena = nullptr; size_t arena_bytes = 0;
-  float4 *prim_bv = nullptr, *prim_tv = nullptr, *prim_mat = nullptr, *sorted_tv = nullptr, *nodes = nullptr;
+  float4 *prim_bv = nullptr, *prim_tv = nullptr, *prim_mat = nullptr, *sorted_tv = nullptr, *nodes = nullptr, *wnodes = nullptr;
   int2* refs = nullptr;        // file-order (type,id)
   uint32_t* tri_prim = nullptr;  // triangle id -> file-order prim index (for rt_scene_update_triangles)
   LightSun* suns = nullptr; LightBulb* bulbs = nullptr; PlaneRec* planes = nullptr;
@@ -90,7 +91,7 @@ struct rt_scene {
   int* node_karras = nullptr;      // [n-1] slot -> reference (Karras) internal index
   float* bounds = nullptr;         // 6 floats (min3,max3) as ordered ints during reduction
   uint32_t* sorted_keys32 = nullptr; uint64_t* sorted_keys64 = nullptr; uint32_t* sorted_perm = nullptr;
-  bool built = false; int built_bits = 0; bool built_topdown = false;
+  bool built = false; int built_bits = 0; bool built_topdown = false, built_wide = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the last build (rt_scene_build_ms)
   // RT_RENDER_OVERLAP_BUILD: the point in the caller's stream before this frame's update/build work
   cudaEvent_t ev_fork = nullptr; cudaStream_t fork_stream = nullptr; bool fork_armed = false;

@@ -758,7 +758,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
       RT_CUDA(cudaEventCreateWithFlags(&st->ev_cnt[k], cudaEventDisableTiming));
     }
     int per_sm = 0, sms = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false, false>, RT_TRAV_THREADS, 0));
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
     if (per_sm < 1) per_sm = 1;
     if (const char* e = getenv("RT_TRAV_CTAS_PER_SM")) { const int v = atoi(e); if (v >= 1 && v < per_sm) per_sm = v; }  // experiments
@@ -769,7 +769,7 @@ int ensure_common(rt_scene* s, RenderState* st) {
 
 RtDeviceScene device_scene(const rt_scene* s) {
   RtDeviceScene d;
-  d.n = s->n; d.root = (const int*)(s->bounds + 8); d.nodes = s->nodes; d.sorted_tv = s->sorted_tv; d.perm = s->sorted_perm; d.prim_mat = s->prim_mat;
+  d.n = s->n; d.root = (const int*)(s->bounds + 8); d.nodes = s->nodes; d.wnodes = (s->built_wide && !getenv("RT_NO_WIDE")) ? s->wnodes : nullptr; d.sorted_tv = s->sorted_tv; d.perm = s->sorted_perm; d.prim_mat = s->prim_mat;
   d.suns = s->suns; d.num_suns = s->cfg.num_suns; d.bulbs = s->bulbs; d.num_bulbs = s->cfg.num_bulbs;
   d.planes = s->planes; d.num_planes = s->cfg.num_planes;
   return d;
@@ -781,16 +781,33 @@ int lane_of(unsigned flags) {
 // one traversal of a two-ended ray queue (slots [0, nf) and [cap - nb, cap)): the lane's kernel on each end, then
 // (exact lane) the reference-order pass over the rays whose certificate failed.  Returns the number of launches.
 // ctr: [0] fetch ticket front, [3] fallback count, [4] fallback fetch ticket, [6] fetch ticket back.
+template <bool EXACT, bool WIDE>
+void launch_near_w(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
+                   float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
+  if (sun) {
+    if (count) traverse_near_kernel<EXACT, true, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_near_kernel<EXACT, false, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  } else {
+    if (count) traverse_near_kernel<EXACT, true, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_near_kernel<EXACT, false, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  }
+}
 template <bool EXACT>
 void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
                  float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
-  if (sun) {
-    if (count) traverse_near_kernel<EXACT, true, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
-    else traverse_near_kernel<EXACT, false, true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
-  } else {
-    if (count) traverse_near_kernel<EXACT, true, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
-    else traverse_near_kernel<EXACT, false, false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  if (sc.wnodes && sc.n > 1) {
+    static int wide_per_sm[2] = {0, 0};  // the wide kernels hold more registers: fewer resident CTAs, hence a smaller persistent grid
+    int& w = wide_per_sm[sun ? 1 : 0];
+    if (w == 0) {
+      if (sun) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&w, traverse_near_kernel<EXACT, false, true, true>, RT_TRAV_THREADS, 0);
+      else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&w, traverse_near_kernel<EXACT, false, false, true>, RT_TRAV_THREADS, 0);
+      if (w < 1) w = 1;
+    }
+    int sms = 148; { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    grid = std::min(grid, sms * w);
+    launch_near_w<EXACT, true>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
   }
+  else launch_near_w<EXACT, false>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
 }
 // counts_dev == nullptr: nf / nb are the ray counts (the host read them back).  counts_dev != nullptr (a pass queued without host
 // round trips): the kernels read the counts from counts_dev[1] (front) and counts_dev[5] (back); nf / nb only say which

@@ -177,6 +177,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes ? bytes : 16); return o; };
   size_t o_bv = carve(n1 * 48), o_tv = carve(n1 * 48), o_mat = carve(n1 * 48), o_stv = carve(n1 * 16 * RT_TV_STRIDE), o_nodes = carve(n1 * 64);
+  size_t o_wn = carve(n1 * 128);
   size_t o_refs = carve(n1 * 8), o_tp = carve((size_t)(s->nt > 0 ? s->nt : 1) * 4);
   size_t o_sun = carve((size_t)d->num_suns * sizeof(LightSun)), o_bulb = carve((size_t)d->num_bulbs * sizeof(LightBulb)),
          o_pl = carve((size_t)d->num_planes * sizeof(PlaneRec));
@@ -188,7 +189,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   if (e != cudaSuccess) { rt_set_error(std::string("rt_scene_create: arena cudaMalloc: ") + cudaGetErrorString(e)); delete s; return RT_ERR_NOMEM; }
   char* A = s->arena;
   s->prim_bv = (float4*)(A + o_bv); s->prim_tv = (float4*)(A + o_tv); s->prim_mat = (float4*)(A + o_mat);
-  s->sorted_tv = (float4*)(A + o_stv); s->nodes = (float4*)(A + o_nodes); s->refs = (int2*)(A + o_refs);
+  s->sorted_tv = (float4*)(A + o_stv); s->nodes = (float4*)(A + o_nodes); s->wnodes = (float4*)(A + o_wn); s->refs = (int2*)(A + o_refs);
   s->tri_prim = (uint32_t*)(A + o_tp); s->suns = (LightSun*)(A + o_sun); s->bulbs = (LightBulb*)(A + o_bulb);
   s->planes = (PlaneRec*)(A + o_pl); s->keys_a = (uint64_t*)(A + o_ka); s->keys_b = (uint64_t*)(A + o_kb);
   s->perm_a = (uint32_t*)(A + o_pa); s->perm_b = (uint32_t*)(A + o_pb); s->hist = (uint32_t*)(A + o_hist);

@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 #ifndef RT_TRAV_MIN_CTAS
 #define RT_TRAV_MIN_CTAS 1
 #endif
-template <bool EXACT, bool COUNT, bool SUN>
+template <bool EXACT, bool COUNT, bool SUN, bool WIDE>
 __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
                                                                        const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
@@ -525,7 +525,39 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, RT_TRAV_MIN_CTAS) traverse_ne
       }
     }
 #else
-    if (!leaf_phase && act && !atleaf) {
+    if (WIDE && !leaf_phase && act && !atleaf) {
+      // ---- node phase, 4-wide tree (RT_BUILD_WIDE4, experimental): one step = the four grandchildren ----
+      // Half the dependent steps per ray for the same box tests (profiles/wide_tree_steps_r01.json).  Every child is
+      // tested exactly like a child of the binary step (order-independent box test, slack-inflated culling key), so
+      // the set of leaves reached differs from the binary lane's only by subtrees the intermediate node would have
+      // culled — and the exact lane's answer does not depend on the order or the tree (its definition is on leaves).
+      if (COUNT) n_nodes++;
+      const float4* np = sc.wnodes + 8 * (size_t)cur;
+      float e[4], k[4]; unsigned rf[4];
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        float4 a, b;
+        rt_ld256(np + 2 * c, a, b);
+        V3 tn;
+        bool h = rt_slab_tn2<true>(a, b, q2, (EXACT || SUN) ? INFINITY : tmax, e[c], tn);  // a NaN box (unused place) fails
+        rf[c] = __float_as_uint(b.z);
+        k[c] = e[c];
+        if (EXACT && !SUN) { k[c] = rt_key_inflated(tn, b.w, rt_ray2_inv(q2), omk); h = h && !(k[c] > tcut); }
+        if (!h) e[c] = INFINITY;  // sorts last; a box that passes is never entered at +INF
+      }
+      // ascending by entry distance: (0,1) (2,3) (0,2) (1,3) (1,2)
+#define RT_CSWAP(i_, j_) do { if (e[j_] < e[i_]) { const float te_ = e[i_]; e[i_] = e[j_]; e[j_] = te_; const float tk_ = k[i_]; k[i_] = k[j_]; k[j_] = tk_; \
+                                                   const unsigned tr_ = rf[i_]; rf[i_] = rf[j_]; rf[j_] = tr_; } } while (0)
+      RT_CSWAP(0, 1); RT_CSWAP(2, 3); RT_CSWAP(0, 2); RT_CSWAP(1, 3); RT_CSWAP(1, 2);
+#undef RT_CSWAP
+      // the nearest hit child next, the others on the stack with the nearest of them on top
+      if (e[3] < INFINITY) RT_PUSH(rf[3], k[3]);
+      if (e[2] < INFINITY) RT_PUSH(rf[2], k[2]);
+      if (e[1] < INFINITY) RT_PUSH(rf[1], k[1]);
+      cur = rf[0];
+      need_pop = !(e[0] < INFINITY);
+    }
+    if (!WIDE && !leaf_phase && act && !atleaf) {
       // ---- node phase ----
       if (COUNT) n_nodes++;
       const float4* np = sc.nodes + 4 * (size_t)cur;

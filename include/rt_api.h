@@ -75,9 +75,14 @@ enum {
                                   193-200 accumulates and drops)                                  */
   RT_BUILD_TOPDOWN      = 2u,  /* per-node Karras range/split search (lbvh_builder.cu:103-322) +
                                   separate refit instead of the fused bottom-up builder           */
-  RT_BUILD_LOCAL_CLIMB  = 4u   /* fused bottom-up builder whose levels inside a 512-leaf chunk meet in shared
+  RT_BUILD_LOCAL_CLIMB  = 4u,  /* fused bottom-up builder whose levels inside a 512-leaf chunk meet in shared
                                   memory (default: every level through global atomics); same tree,
                                   measured no faster (the primitive gather bounds the kernel), kept for A/B */
+  RT_BUILD_WIDE4        = 8u   /* EXPERIMENTAL: after the LBVH, derive a 4-wide tree over the same leaves (a node's
+                                  children = its grandchildren, 128-byte nodes).  The near-first lanes of rt_render /
+                                  rt_trace then step through it (half the dependent steps per ray); the exported
+                                  LBVH, the reference-order lane and the exact lane's fallback keep the binary tree.
+                                  Same hit ids: the exact lane's answer is defined on leaves      */
 };
 int rt_build_lbvh(rt_scene* scene, int morton_bits, unsigned flags, void* stream, float* ms_out);
 /* Device time of the last rt_build_lbvh (the number lbvh_builder.cu:489 prints), read AFTER the fact so

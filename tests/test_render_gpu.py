@@ -445,3 +445,40 @@ def test_pass_schedules_give_the_same_pixels(monkeypatch):
                     assert np.array_equal(r["rgba"], ref["rgba"]) and np.array_equal(r["ids"], ref["ids"]) and np.array_equal(r["written"], ref["written"])
                     assert r["counters"].rays == ref["counters"].rays and r["counters"].samples == ref["counters"].samples
                     assert r["counters"].wavefront_iters >= ref["counters"].wavefront_iters - 0  # queued passes count non-empty iterations like the host loop
+
+
+def test_wide4_tree_gives_the_same_hits():
+    """RT_BUILD_WIDE4 (experimental): the near-first lanes step through a 4-wide tree whose nodes hold a binary node's
+    grandchildren.  The exact lane's answer is defined on leaves, so ids, distances and images must equal the
+    reference-order lane (which keeps the binary tree) bit for bit: triangles, spheres, a mixed scene with duplicate
+    codes, the redchair mesh (shared edges: certificate and fallback at work), tiny trees."""
+    scenes = []
+    for gen in (synth.soup, synth.spheres):
+        cfg, a = gen(100_000, seed=2, width=160, height=120, aa=0)
+        scenes.append(H.oracle_from_arrays(cfg, synth.finish_triangles(a)))
+    cfg, a = H.mixed_scene(5000)
+    scenes.append(H.oracle_from_arrays(cfg, a))
+    for n in (2, 3, 5, 9):
+        cfg, a = synth.soup(n, seed=n, width=32, height=32, aa=0)
+        scenes.append(H.oracle_from_arrays(cfg, synth.finish_triangles(a)))
+    p = H.scene_path("redchair")
+    if p is not None:
+        scenes.append(O.OracleScene(p))
+    org, d = random_rays(300_000, 5, 2.0)
+    for o in scenes:
+        o.build(O.BOUNDS_COMPUTED, 30)
+        sc = H.gpu_scene_from_oracle(o, O.BOUNDS_COMPUTED)
+        sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED | api.BUILD_WIDE4)
+        ri, rt_, _ = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER)
+        wi, wt, cw = gpu_trace(sc, org, d, api.COUNTERS)
+        assert np.array_equal(wi, ri) and np.array_equal(wt.view(np.uint32), rt_.view(np.uint32)), "%d rays differ" % (wi != ri).sum()
+        for aa, (w, h) in ((0, (200, 150)), (32, (64, 48))):
+            a0 = sc.render(w, h, aa, api.TRAVERSE_REF_ORDER, want_ids=True); a1 = sc.render(w, h, aa, 0, want_ids=True)
+            assert np.array_equal(a0["ids"], a1["ids"]) and np.array_equal(a0["rgba"], a1["rgba"]) and a0["counters"].rays == a1["counters"].rays
+        sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)  # the binary tree alone: same answers, about twice the steps
+        bi, bt, cb = gpu_trace(sc, org, d, api.COUNTERS)
+        assert np.array_equal(bi, ri) and np.array_equal(bt.view(np.uint32), rt_.view(np.uint32))
+        if o.counts()["prims"] > 1000:
+            print("steps per ray: binary %.2f, 4-wide %.2f" % (cb.nodes_visited / len(org), cw.nodes_visited / len(org)))
+            assert cw.nodes_visited < 0.75 * cb.nodes_visited
+        sc.close()
