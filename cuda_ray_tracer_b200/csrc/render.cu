@@ -973,7 +973,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (P.mode == 2) { rc = ensure_rng_tables(rs, std::max(32, P.spp), 0); if (rc) return rc; }
   else if (P.need_rng) { rc = ensure_rng_tables(rs, 256, (int)((npx + 255) / 256)); if (rc) return rc; }
 
-  // pass size: all per-sample state of a pass lives in one pool (RT_POOL_BYTES each, default 6 GB)
+  // pass size: all per-sample state of a pass lives in one pool (RT_POOL_BYTES each)
   const size_t per_sample = 32 + 16 + 4 + (size_t)P.depth * 64 + 2 * 32 + 8 + 4;
   // 16 GB per pool (two pools): the 4K x 16 spp frame is two passes = 4 traverse launches instead of 12 with 6 GB pools,
   // and every launch costs ~0.46 ms whatever its size (measured 47.6 -> 46.6 ms per frame).  A B200 has 180 GB; on a
@@ -990,13 +990,12 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (npix_pass >= nslots) npix_pass = nslots;
   else npix_pass = std::max<long long>(32, npix_pass & ~31ll);
   // TWO PASSES IN FLIGHT.  Every traverse launch pays ~0.46 ms whatever its size (scripts/launch_fixed_cost.py): the
-  // kernel cannot end before its longest rays have, a ray is a chain of dependent node fetches, and the longest of
-  // 25 M rays is ~30x the mean, so the last ~0.4 ms of a launch keep a handful of warps busy on an otherwise empty
-  // GPU.  Passes are independent (disjoint pixels), so two of them run on two streams with a pool each: while one
-  // pass drains, the CTAs of the other pass's kernels fill the SMs it leaves.  The host alternates between the two
-  // (it blocks on one pass's ray counts while the other pass's kernels are queued), so neither stream runs dry.
-  // Same pixels: a pass is the same computation on
-  // whichever stream it runs (tests/test_render_gpu.py::test_multi_pass_equals_single_pass and the parity suite).
+  // kernel cannot end before its longest rays have, a ray is a chain of dependent node fetches, and the longest of a
+  // launch's rays takes ~30x the mean number of steps.  Passes are independent (disjoint pixels), so two of them run on
+  // two streams with a pool each and the kernels of one fill what the other leaves idle: 47.9 -> 46.6 ms on the 4K
+  // frame.  (Less than the 4 x 0.46 ms the drains add up to: every resident CTA holds one of the long rays, so the SMs
+  // free up late.)  Same pixels: a pass is the same computation on whichever stream it runs
+  // (tests/test_render_gpu.py::test_pass_schedules_give_the_same_pixels, test_multi_pass_equals_single_pass).
   const bool serial = (flags & RT_RENDER_SERIAL_PASSES) != 0 || getenv("RT_SERIAL_PASSES") != nullptr;
   // A frame that fits one pass stays one pass: splitting it in two hides one drain and pays two more launches
   // (measured: 24.2 ms as one pass, 25.0 ms as two half passes in flight on a 1/2 slice of the 4K frame).
