@@ -372,8 +372,8 @@ def run_b200(a):
     build_alone = min(sc.build_lbvh_karas(30, bflags) for _ in range(3))  # nothing else on the GPU
     sc.render_device(W, Hh, spp, img_d, flags=(rflags & ~api.TIME_TRAVERSE) | api.COUNTERS, tiles=tiles, counters=cnt)
     torch.cuda.synchronize()
-    alg = torch.tensor([node_bytes * cnt.nodes_visited + 48.0 * cnt.leaf_tests, float(cnt.nodes_visited), float(cnt.leaf_tests), float(cnt.rays)],
-                       dtype=torch.float64, device=dev)
+    alg = torch.tensor([node_bytes * cnt.nodes_visited + 48.0 * cnt.leaf_tests, float(cnt.nodes_visited), float(cnt.leaf_tests), float(cnt.rays),
+                        float(cnt.packet_steps)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(alg, op=dist.ReduceOp.SUM)
     # diagnostics for the scaling figure: per-rank render time of one frame (load balance) and the cost of the gather alone
@@ -432,6 +432,7 @@ def run_b200(a):
         "lbvh_build_ms_alone": build_alone,   # best of 3 with an idle GPU and a synchronising call
         "rays_per_step": dev_res["rays"] / a.steps,
         "nodes_per_ray": alg[1].item() / max(alg[3].item(), 1), "leaf_tests_per_ray": alg[2].item() / max(alg[3].item(), 1),
+        "packet_lanes_per_node_step": (alg[1].item() / alg[4].item()) if alg[4].item() > 0 else None,  # of 32: lanes that wanted the node their warp fetched
         "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 3 * 12 * n, "d2h_bytes_per_step": W * Hh * 4,
                 "ms_per_step": e2e_res["ms"] / a.steps},
         "gpu_launches": int(dev_res["launches"]),

@@ -18,6 +18,7 @@ LIB_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libb200rt.so")  # RT
 
 BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN, BUILD_LOCAL_CLIMB, BUILD_WIDE4 = 0, 1, 2, 4, 8
 SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE, TRAVERSE_REF_ORDER, RENDER_OVERLAP_BUILD, RENDER_SERIAL_PASSES = 0, 1, 2, 4, 8, 16, 32, 64, 128
+TRAVERSE_PACKET, TRAVERSE_PER_RAY = 256, 512
 
 
 class RtError(RuntimeError):
@@ -50,7 +51,7 @@ class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("nodes_visited", C.c_uint64), ("leaf_tests", C.c_uint64),
                 ("shaded_hits", C.c_uint64), ("wavefront_iters", C.c_uint32), ("passes", C.c_uint32), ("render_ms", C.c_float),
                 ("kernel_launches", C.c_uint32), ("traverse_ms", C.c_float), ("traverse_launches", C.c_uint32),
-                ("fallback_rays", C.c_uint64)]
+                ("fallback_rays", C.c_uint64), ("packet_steps", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -212,7 +212,6 @@ __global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams
 #define RT_GEN_CHUNKS 4   // a block generates 4 x 256 consecutive samples: the 12.8 KB skip-ahead table is staged once
 __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
   __shared__ uint32_t s_nib[RT_RNG_NIB_STRIDE];
-  __shared__ unsigned s_app[2 * 8 + 2];
   const long long base = (long long)blockIdx.x * (256 * RT_GEN_CHUNKS);
   // sample-major order (i = sample * npix + pixel slot): a block almost always lies inside one sample index,
   // whose skip-ahead matrix all its threads share
@@ -222,19 +221,26 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
     for (int k = threadIdx.x; k < RT_RNG_NIB_STRIDE / 4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
     __syncthreads();
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0) B.counters[1] = P.cam.bounces != 0 ? (unsigned)P.S : 0u;  // primary rays sit at their sample's slot
   for (int chunk = 0; chunk < RT_GEN_CHUNKS; chunk++) {
-  const long long i_ll = base + chunk * 256 + threadIdx.x;
+  const long long g_ll = base + chunk * 256 + threadIdx.x;  // thread order: sample-major (g = sample * npix + pixel slot)
   if (base + chunk * 256 >= P.S) break;  // block-uniform
-  const int i = (int)i_ll;
-  bool live = i < P.S;
+  const bool in_range = g_ll < P.S;
+  bool live = in_range;
   int s = 0, lp = 0, x = 0, y = 0, pix = 0;
   if (live) {
-    s = i / P.npix; lp = i - s * P.npix;
+    s = (int)(g_ll / P.npix); lp = (int)(g_ll - (long long)s * P.npix);
     live = slot_to_pixel(P, P.slot0 + lp, x, y, pix);
   }
+  // SAMPLE ID (state index, queue slot of the primary ray, ray tag): pixel-major, i = pixel slot * spp + sample, so
+  // that the 32 consecutive rays a warp of the traversal kernel fetches are the samples of ONE or two pixels — the
+  // reference's own mapping (one warp = one pixel's 32 samples, draw.cu:135-213).  Such rays walk the same nodes:
+  // their fetches fall into the same 128-byte lines (one L1TEX wavefront instead of 32) and they reach their leaves
+  // together.  Shadow rays inherit the order through the shade kernel's appends.
+  const int i = lp * P.spp + s;
   bool has = false; V3 eye = mk3(0, 0, 0), dir = mk3(0, 0, 0);
   // a sample that emits a primary ray is initialised by the first shade visit (shade_kernel<.., FIRST = true>)
-  if (i < P.S && !(live && P.cam.bounces != 0)) {
+  if (in_range && !(live && P.cam.bounces != 0)) {
     B.accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (P.full_shade) B.ctl[i] = 0u;
   }
@@ -299,7 +305,14 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
       has = true;
     } else if (hit_id_out && s == 0) hit_id_out[pix] = -1;
   }
-  queue_append_block<8>(qout, B.counters + 1, B.counters + 5, (unsigned)P.S, has, eye, dir, INFINITY, (unsigned)i, s_app);
+  // no compaction: the ray of sample i goes to queue slot i (a sample without a ray leaves a record the traversal and
+  // shade kernels skip); the live rays are counted for the accounting, one atomic per block
+  if (in_range && P.cam.bounces != 0) {
+    qout[2 * (size_t)i] = make_float4(eye.x, eye.y, eye.z, INFINITY);
+    qout[2 * (size_t)i + 1] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(has ? (unsigned)i : RT_RAY_DEAD));
+  }
+  const int nlive = __syncthreads_count(has);
+  if (nlive && threadIdx.x == 0) atomicAdd(B.counters + 7, (unsigned)nlive);
   }
 }
 
@@ -372,9 +385,11 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
   for (unsigned g0 = blockIdx.x * blockDim.x; g0 < n_front + n_back; g0 += gridDim.x * blockDim.x) {  // block-uniform
   const unsigned g = g0 + threadIdx.x;
   bool emit = false, shaded = false; V3 eo = mk3(0, 0, 0), ed = mk3(0, 0, 0); float elimit = INFINITY; unsigned etag = 0u;
-  if (g < n_front + n_back) {
-    const unsigned r = g < n_front ? g : (unsigned)P.S - n_back + (g - n_front);  // queue slot: front end, then back end
-    const float4 q0 = __ldcs(qin + 2 * (size_t)r), q1 = __ldcs(qin + 2 * (size_t)r + 1);
+  const unsigned r = g < n_front ? g : (unsigned)P.S - n_back + (g - n_front);  // queue slot: front end, then back end
+  float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(RT_RAY_DEAD));
+  if (g < n_front + n_back) { q0 = __ldcs(qin + 2 * (size_t)r); q1 = __ldcs(qin + 2 * (size_t)r + 1); }
+  // RT_RAY_DEAD: a sample without a primary ray (generate_kernel leaves such a record at the sample's slot)
+  if (__float_as_uint(q1.w) != RT_RAY_DEAD) {
     const float2 hv = __ldcs(B.hits + r);
     const V3 o = mk3(q0.x, q0.y, q0.z), d = mk3(q1.x, q1.y, q1.z);
     const int i = (int)(__float_as_uint(q1.w) & ~RT_RAY_ANYHIT);
@@ -454,9 +469,9 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
       // T_W_PRIMARY / T_W_GI / T_W_REFLECT / T_W_REFRACT2: the "if hit" body
       const unsigned flag = hdr >> 24;
       if (type == T_W_PRIMARY && hit_id_out) {
-        const int s = i / P.npix;
-        if (s == 0) {
-          int x, y, pix; slot_to_pixel(P, P.slot0 + (i - s * P.npix), x, y, pix);
+        const int lp = i / P.spp;  // sample ids are pixel-major (generate_kernel)
+        if (i - lp * P.spp == 0) {
+          int x, y, pix; slot_to_pixel(P, P.slot0 + lp, x, y, pix);
           int out_id = hid;
           if (hid >= 0) out_id = (int)__ldg(sc.perm + ((unsigned)hid & RT_LEAF_MASK));
           hit_id_out[pix] = out_id;
@@ -667,7 +682,7 @@ __global__ void __launch_bounds__(128) resolve_kernel(const RenderParams P, cons
   if (lp >= P.npix) return;
   int x, y, pix;
   if (!slot_to_pixel(P, P.slot0 + lp, x, y, pix)) return;
-  const float4* a = B.accum + lp;
+  const float4* a = B.accum + (size_t)lp * P.spp;  // the pixel's samples are consecutive (sample id = pixel slot * spp + sample)
   uchar4 out;
   if (P.mode != 2) {  // render_kernel store, draw.cu:129-132 (float -> unsigned char truncates)
     const float4 c = a[0];
@@ -676,7 +691,7 @@ __global__ void __launch_bounds__(128) resolve_kernel(const RenderParams P, cons
   } else {
     int np2 = 1; while (np2 < P.spp) np2 <<= 1;
     float4 v;
-    const size_t st = (size_t)P.npix;
+    const size_t st = 1;
     if (np2 <= 2) v = tree_sum<2>(a, st, P.spp);
     else if (np2 == 4) v = tree_sum<4>(a, st, P.spp);
     else if (np2 == 8) v = tree_sum<8>(a, st, P.spp);
@@ -684,7 +699,7 @@ __global__ void __launch_bounds__(128) resolve_kernel(const RenderParams P, cons
     else if (np2 == 32) v = tree_sum<32>(a, st, P.spp);
     else if (np2 == 64) v = tree_sum<64>(a, st, P.spp);
     else {  // in-place halving in global memory (the accumulators are dead after this kernel)
-      float4* w = B.accum + lp;
+      float4* w = B.accum + (size_t)lp * P.spp;
       for (int half = np2 / 2; half >= 1; half >>= 1)
         for (int k = 0; k < half; k++) {
           const float4 lo = k < P.spp ? w[(size_t)k * st] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -816,6 +831,35 @@ void launch_near_w(bool count, bool sun, int grid, cudaStream_t st, const RtDevi
     else traverse_near_kernel<EXACT, false, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
   }
 }
+// the packet kernel's persistent grid: every SM full
+template <bool EXACT>
+int packet_grid(bool sun) {
+  static int g[2] = {0, 0};
+  int& w = g[sun ? 1 : 0];
+  if (w == 0) {
+    int per_sm = 0, sms = 148, dev = 0;
+    if (sun) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_packet_kernel<EXACT, false, true>, RT_PKT_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_packet_kernel<EXACT, false, false>, RT_PKT_THREADS, 0);
+    cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("RT_PKT_CTAS_PER_SM")) { const int v = atoi(e); if (v >= 1 && v < per_sm) per_sm = v; }  // experiments
+    w = sms * per_sm;
+  }
+  return w;
+}
+template <bool EXACT>
+void launch_packet(bool count, bool sun, long long n_hint, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
+                   float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
+  int grid = packet_grid<EXACT>(sun);
+  if (n_hint >= 0) grid = (int)std::max<long long>(1, std::min<long long>(grid, (n_hint + RT_PKT_THREADS - 1) / RT_PKT_THREADS));
+  if (sun) {
+    if (count) traverse_packet_kernel<EXACT, true, true><<<grid, RT_PKT_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_packet_kernel<EXACT, false, true><<<grid, RT_PKT_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  } else {
+    if (count) traverse_packet_kernel<EXACT, true, false><<<grid, RT_PKT_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    else traverse_packet_kernel<EXACT, false, false><<<grid, RT_PKT_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  }
+}
 template <bool EXACT>
 void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
                  float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
@@ -836,8 +880,11 @@ void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDevice
 // counts_dev == nullptr: nf / nb are the ray counts (the host read them back).  counts_dev != nullptr (a pass queued without host
 // round trips): the kernels read the counts from counts_dev[1] (front) and counts_dev[5] (back); nf / nb only say which
 // ends can hold rays at all (0 = skip the launch), and the grids are the full persistent grid.
+// packet: the rays of this queue are coherent in queue order (primary rays and the shadow rays of their hits): one warp
+// walks the tree once for 32 consecutive rays (traverse_packet_kernel) instead of 32 independent lanes
 int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned nf, unsigned nb,
-                    unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list, const unsigned* counts_dev = nullptr) {
+                    unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list, const unsigned* counts_dev = nullptr,
+                    bool packet = false) {
   int launches = 0;
   for (int end = 0; end < 2; end++) {
     const unsigned n = end ? nb : nf, first = end ? cap - nb : 0u;
@@ -849,6 +896,10 @@ int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const R
     if (lane == RT_LANE_REF) {
       if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
       else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
+    } else if (packet && sc.n > 0) {
+      const long long n_hint = counts_dev ? -1ll : (long long)n;
+      if (lane == RT_LANE_NEAR) launch_packet<false>(count, end == 1, n_hint, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
+      else launch_packet<true>(count, end == 1, n_hint, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
     } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
     else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
     launches++;
@@ -959,6 +1010,9 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;
   const bool time_trav = (flags & (RT_COUNTERS | RT_TIME_TRAVERSE)) != 0;
+  // packet traversal: 0 never, 1 coherent queues (primary rays; every ray of a scene without mirrors, glass or GI), 2 always
+  int pkt_mode = (flags & RT_TRAVERSE_PER_RAY) ? 0 : (flags & RT_TRAVERSE_PACKET) ? 2 : 1;
+  if (const char* e = getenv("RT_PACKET")) pkt_mode = atoi(e);  // experiments
   const bool both = s->any_shiny && s->any_trans;
   const int gi = s->cfg.gi != 0 ? 1 : 0;
   P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
@@ -1087,7 +1141,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     samples += (uint64_t)c.P.S;
     // the very first pass of the frame may run its head on the build-overlap stream
     cudaStream_t gs = (!head_joined && c.st == st) ? hs : c.st;
-    RT_PASS_CUDA(cudaMemsetAsync(c.counters, 0, 8, gs));
+    RT_PASS_CUDA(cudaMemsetAsync(c.counters, 0, 32, gs));
     if (c.P.mode != 2 && c.P.need_rng) {
       const int hn = (int)(((npx + 255) / 256 + 31) & ~31ll);
       rng_init_pixels_kernel<<<(unsigned)(((long long)hn * 256 + 255) / 256), 256, 0, gs>>>(c.P, c.B, hn);
@@ -1101,7 +1155,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       RT_PASS_CUDA(cudaStreamWaitEvent(c.st, rs->ev_join, 0));
       head_joined = true;
     }
-    RT_PASS_CUDA(cudaMemcpyAsync(c.h_count, c.counters + 1, 4, cudaMemcpyDeviceToHost, c.st));
+    RT_PASS_CUDA(cudaMemcpyAsync(c.h_count, c.counters + 1, 28, cudaMemcpyDeviceToHost, c.st));  // [1] slots to scan, [7] rays among them
     RT_PASS_CUDA(cudaEventRecord(c.ev_cnt, c.st));
     c.active = true; c.after_gen = true; c.qin = c.B.qa; c.qout = c.B.qb; c.iter_in_pass = 0;
     return RT_OK;
@@ -1109,21 +1163,24 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   // the ray counts context c asked for are in: queue its next wavefront iteration, or finish the pass and start another
   auto advance = [&](PassCtx& c) -> int {
     RT_PASS_CUDA(cudaEventSynchronize(c.ev_cnt));
-    if (c.after_gen) { c.n_front = c.h_count[0]; c.n_back = 0; c.after_gen = false; }  // primary rays all go to the front end
+    uint64_t nrays_iter = 0;
+    if (c.after_gen) { c.n_front = c.h_count[0]; c.n_back = 0; c.after_gen = false; nrays_iter = c.h_count[6]; }  // primary rays: front end, slot = sample id
     else {
       fb_rays += c.h_count[2];
       if (time_trav) { float ms = 0.f; RT_PASS_CUDA(cudaEventElapsedTime(&ms, c.t0, c.t1)); trav_ms += ms; }
       c.n_front = c.h_count[0]; c.n_back = c.h_count[4];
       if (c.h_count[1]) { rt_set_error("rt_render: continuation stack overflow (more nested bounces than the stack was sized for)"); return RT_ERR_INVALID; }
       std::swap(c.qin, c.qout);
+      nrays_iter = (uint64_t)c.n_front + c.n_back;
     }
     const unsigned n_front = c.n_front, n_back = c.n_back;
     if (n_front + n_back > 0) {
-      iters++; rays += (uint64_t)n_front + n_back;
+      iters++; rays += nrays_iter;
       RT_PASS_CUDA(cudaMemsetAsync(c.counters, 0, 28, c.st));
       if (time_trav) RT_PASS_CUDA(cudaEventRecord(c.t0, c.st));
+      const bool pkt = pkt_mode == 2 || (pkt_mode == 1 && (c.iter_in_pass == 0 || !P.full_shade));
       const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, c.st, sc, (const float4*)c.qin, n_front, n_back, (unsigned)c.P.S, c.B.hits,
-                                     c.counters, rs->stats, c.B.fb_list);
+                                     c.counters, rs->stats, c.B.fb_list, nullptr, pkt);
       launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);  // the (near-empty) fallback pass is not a traversal launch of its own
       if (time_trav) RT_PASS_CUDA(cudaEventRecord(c.t1, c.st));
       {
@@ -1198,7 +1255,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
         const unsigned may_front = it == 0 ? 1u : (s->cfg.num_bulbs > 0 ? 1u : 0u), may_back = it == 0 ? 0u : (s->cfg.num_suns > 0 ? 1u : 0u);
         if (time_trav) RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + it)], c.st));
         const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, c.st, sc, (const float4*)qin, may_front, may_back, (unsigned)c.P.S, c.B.hits,
-                                       blk, rs->stats, c.B.fb_list, blk);
+                                       blk, rs->stats, c.B.fb_list, blk, pkt_mode != 0);
         launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);
         if (time_trav) RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + it) + 1], c.st));
         RenderBuffers Bn = c.B; Bn.counters = blk + 16;  // this iteration's shade appends the next iteration's rays
@@ -1236,7 +1293,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     for (long long pi = 0; pi < npasses_total; pi++)
       for (int it = 0; it <= nl; it++) {
         const uint32_t* blk = rs->h_blocks + 256 * pi + 16 * it;
-        const uint64_t nr = (uint64_t)blk[1] + blk[5];
+        const uint64_t nr = it == 0 ? (uint64_t)blk[7] : (uint64_t)blk[1] + blk[5];  // block 0: [1] = slots scanned, [7] = primary rays among them
         if (nr) iters++;
         rays += nr; fb_rays += blk[3];
         overflow = overflow || blk[16 + 2] != 0u;
@@ -1250,9 +1307,9 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     counters->kernel_launches = launches; counters->traverse_ms = trav_ms; counters->traverse_launches = trav_launches;
     counters->fallback_rays = fb_rays;
     RT_CUDA(cudaEventElapsedTime(&counters->render_ms, rs->e0, rs->e1));
-    unsigned long long hs[3];
-    RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
-    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1]; counters->shaded_hits = hs[2];
+    unsigned long long hs[10];
+    RT_CUDA(cudaMemcpy(hs, rs->stats, 80, cudaMemcpyDeviceToHost));
+    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1]; counters->shaded_hits = hs[2]; counters->packet_steps = hs[9];
 #ifdef RT_LANE_STATS
     if (count) {
       unsigned long long q[9]; RT_CUDA(cudaMemcpy(q, rs->stats, 72, cudaMemcpyDeviceToHost));
@@ -1308,7 +1365,7 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, rs->trace_q);
   RT_CUDA(cudaEventRecord(rs->e0, st));
   launch_traverse(lane_of(flags), count, rs->trav_grid, st, sc, (const float4*)rs->trace_q, (unsigned)n, 0u, (unsigned)n, rs->trace_hits, rs->counters,
-                  rs->stats, rs->trace_fb);
+                  rs->stats, rs->trace_fb, nullptr, (flags & RT_TRAVERSE_PACKET) != 0);  // arbitrary rays: per-ray lanes unless the caller says they are coherent
   RT_CUDA(cudaEventRecord(rs->e1, st));
   unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(rs->trace_hits, s->sorted_perm, n, d_hit_id, d_hit_t);
   RT_CUDA(cudaGetLastError());
@@ -1318,9 +1375,9 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
     counters->rays = (uint64_t)n; counters->kernel_launches = 3; counters->traverse_launches = 1;
     RT_CUDA(cudaEventElapsedTime(&counters->traverse_ms, rs->e0, rs->e1));
     counters->render_ms = counters->traverse_ms;
-    unsigned long long hs[3];
-    RT_CUDA(cudaMemcpy(hs, rs->stats, 24, cudaMemcpyDeviceToHost));
-    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1];
+    unsigned long long hs[10];
+    RT_CUDA(cudaMemcpy(hs, rs->stats, 80, cudaMemcpyDeviceToHost));
+    counters->nodes_visited = hs[0]; counters->leaf_tests = hs[1]; counters->packet_steps = hs[9];
     unsigned fb = 0;
     RT_CUDA(cudaMemcpy(&fb, rs->counters + 3, 4, cudaMemcpyDeviceToHost));
     counters->fallback_rays = fb;

@@ -260,6 +260,7 @@ __device__ __forceinline__ RtHit rt_trace_ref(const RtDeviceScene& sc, const V3 
 
 // ray record: q[2r] = (origin.xyz, tlimit), q[2r+1] = (dir.xyz, bits: sample | anyhit << 31)
 #define RT_RAY_ANYHIT 0x80000000u
+#define RT_RAY_DEAD 0x7FFFFFFFu   // tag of a queue slot that holds no ray (generate_kernel: the primary ray of sample i sits at slot i)
 
 #ifndef RT_REFILL_MIN
 #define RT_REFILL_MIN 8      // idle lanes that trigger a refill of the warp
@@ -297,9 +298,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
     if (i < total) {
       const unsigned r = list ? list[i] : first + i;
       const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
-      const RtHit h = rt_trace_ref<COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
-                                          (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
-      __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+      if (__float_as_uint(q1.w) != RT_RAY_DEAD) {
+        const RtHit h = rt_trace_ref<COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
+                                            (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
+        __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+      }
     }
     __syncwarp();
   }
@@ -338,47 +341,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 #define RT_WIDE_SORT 1       // closest-hit rays: 1 = all hit children sorted by entry distance, 0 = nearest next, the rest in child order
                              // (measured: 14.6 instead of 14.0 steps per ray and 4 % slower)
 #endif
-template <bool EXACT, bool COUNT, bool SUN, bool WIDE>
-__global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
-                                                                       const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
-                                                                       unsigned long long* stats, unsigned* __restrict__ fb_list,
-                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
-  // the two values are needed once per chunk of rays: kept in shared memory, not in two registers of every thread
-  // (56 registers = 9 CTAs per SM; 59 = 8)
-  __shared__ unsigned s_range[2];
-  if (threadIdx.x == 0) { const unsigned nn = n_dev ? *n_dev : n_in; s_range[0] = nn; s_range[1] = (n_dev && cap_back) ? cap_back - nn : first_in; }
-  __syncthreads();
-  // stack entry = (reference, culling key): one 64-bit shared-memory access per push / pop (SUN: references only)
-  __shared__ unsigned s_ref[SUN ? RT_STACK_SHARED : 1][RT_TRAV_THREADS];
-  __shared__ uint2 s_ent[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
-  const unsigned lane = threadIdx.x & 31;
-  const int tid = threadIdx.x;
-#ifdef RT_LANE_STATS
-  unsigned long long ls_iter[2] = {0, 0}, ls_lanes[2] = {0, 0}, ls_parked = 0, ls_idle = 0;
-#endif
-  unsigned long long n_nodes = 0, n_leaves = 0;
-  unsigned loc_ref[SUN ? RT_STACK_TOTAL - RT_STACK_SHARED : 1];
-  uint2 loc_ent[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
-  // lane state
-  enum { IDLE = 0, ACTIVE = 1, DONE = 2 };  // ACTIVE: at `cur`; DONE: result ready to be written
-  enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };
-  int st = IDLE;
-  unsigned fl = 0u, r = 0, cur = 0; int sp = 0, best = -1;
-  V3 d = mk3(0, 0, 0);
-  float tlimit = 0.f, tmax = 0.f, omk = 0.f;
-  RtRay2 q2 = rt_ray2(d, d);  // origin and reciprocal direction live only as the packed pairs of the slab test
-  // exact lane, closest-hit rays: tcull = max(tmax, entry distance of the best hit's own leaf box) is what culling
-  // compares with, t2 = smallest accepted distance among the tested primitives other than the best (see below)
-  float tcull = 0.f, t2 = 0.f, tcut = 0.f;  // tcut = tcull * 1.000001 (rounding of the key's products), kept in step
-  // warp state (uniform)
-  unsigned chunk_next = 0, chunk_end = 0; bool exhausted = false;
-
-#define RT_PUSH(ref_, key_)                                                                                       \
-  do {                                                                                                            \
-    if (sp < RT_STACK_SHARED) { if (SUN) s_ref[sp][tid] = (ref_); else s_ent[sp][tid] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
-    else if (sp < RT_STACK_TOTAL) { if (SUN) loc_ref[sp - RT_STACK_SHARED] = (ref_); else loc_ent[sp - RT_STACK_SHARED] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
-    else { fl |= F_FALLBACK; st = DONE; } /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
-  } while (0)
+enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };  // per-ray flags of the near-first kernels
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
 // box on its path is entered before the reference's running tmax at that moment.  Entry distances grow down a
 // path, so that is implied by e_m < t* (e_m = entry of m's own leaf box; "consistent").  When e_m >= t* (the hit
@@ -389,7 +352,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
 // never tested was culled with key > 1.000001 * max(t_b, e_b) of the best b of that moment: if b = m then
 // t_c > e_m; if b != m then t_c > t_b >= t2.  So t2 > e_m proves the claim; otherwise the ray goes to fb_list.
 #define RT_LEAF_TEST(ref_)                                                                                        \
-  do {                                                                                                            \
+do {                                                                                                            \
     if (COUNT) n_leaves++;                                                                                        \
     float th_;                                                                                                    \
     const V3 o = rt_ray2_o(q2);                                                                                   \
@@ -415,6 +378,46 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
     }                                                                                                             \
   } while (0)
 
+template <bool EXACT, bool COUNT, bool SUN, bool WIDE>
+__global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
+                                                                       const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
+                                                                       unsigned long long* stats, unsigned* __restrict__ fb_list,
+                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+  // the two values are needed once per chunk of rays: kept in shared memory, not in two registers of every thread
+  // (56 registers = 9 CTAs per SM; 59 = 8)
+  __shared__ unsigned s_range[2];
+  if (threadIdx.x == 0) { const unsigned nn = n_dev ? *n_dev : n_in; s_range[0] = nn; s_range[1] = (n_dev && cap_back) ? cap_back - nn : first_in; }
+  __syncthreads();
+  // stack entry = (reference, culling key): one 64-bit shared-memory access per push / pop (SUN: references only)
+  __shared__ unsigned s_ref[SUN ? RT_STACK_SHARED : 1][RT_TRAV_THREADS];
+  __shared__ uint2 s_ent[SUN ? 1 : RT_STACK_SHARED][RT_TRAV_THREADS];
+  const unsigned lane = threadIdx.x & 31;
+  const int tid = threadIdx.x;
+#ifdef RT_LANE_STATS
+  unsigned long long ls_iter[2] = {0, 0}, ls_lanes[2] = {0, 0}, ls_parked = 0, ls_idle = 0;
+#endif
+  unsigned long long n_nodes = 0, n_leaves = 0;
+  unsigned loc_ref[SUN ? RT_STACK_TOTAL - RT_STACK_SHARED : 1];
+  uint2 loc_ent[SUN ? 1 : RT_STACK_TOTAL - RT_STACK_SHARED];
+  // lane state
+  enum { IDLE = 0, ACTIVE = 1, DONE = 2 };  // ACTIVE: at `cur`; DONE: result ready to be written
+  int st = IDLE;
+  unsigned fl = 0u, r = 0, cur = 0; int sp = 0, best = -1;
+  V3 d = mk3(0, 0, 0);
+  float tlimit = 0.f, tmax = 0.f, omk = 0.f;
+  RtRay2 q2 = rt_ray2(d, d);  // origin and reciprocal direction live only as the packed pairs of the slab test
+  // exact lane, closest-hit rays: tcull = max(tmax, entry distance of the best hit's own leaf box) is what culling
+  // compares with, t2 = smallest accepted distance among the tested primitives other than the best (see below)
+  float tcull = 0.f, t2 = 0.f, tcut = 0.f;  // tcut = tcull * 1.000001 (rounding of the key's products), kept in step
+  // warp state (uniform)
+  unsigned chunk_next = 0, chunk_end = 0; bool exhausted = false;
+
+#define RT_PUSH(ref_, key_)                                                                                       \
+  do {                                                                                                            \
+    if (sp < RT_STACK_SHARED) { if (SUN) s_ref[sp][tid] = (ref_); else s_ent[sp][tid] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
+    else if (sp < RT_STACK_TOTAL) { if (SUN) loc_ref[sp - RT_STACK_SHARED] = (ref_); else loc_ent[sp - RT_STACK_SHARED] = make_uint2((ref_), __float_as_uint(key_)); sp++; } \
+    else { fl |= F_FALLBACK; st = DONE; } /* the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide */ \
+  } while (0)
   while (true) {
     bool act = st == ACTIVE, atleaf = act && (cur & RT_LEAF_BIT);
     unsigned actm = __ballot_sync(0xffffffffu, act), leafm = __ballot_sync(0xffffffffu, atleaf);
@@ -443,9 +446,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
         if (!exhausted) {
           const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(free_m);
           const unsigned take = min(avail, want), rank = (unsigned)__popc(free_m & ((1u << lane) - 1u));
-          if (st == IDLE && rank < take) {
-            r = chunk_next + rank;
-            const float4 q0 = __ldcs(rays + 2 * (size_t)r), q1 = __ldcs(rays + 2 * (size_t)r + 1);
+          bool fetch = st == IDLE && rank < take;
+          float4 q1 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (fetch) { r = chunk_next + rank; q1 = __ldcs(rays + 2 * (size_t)r + 1); fetch = __float_as_uint(q1.w) != RT_RAY_DEAD; }  // DEAD: no ray in this slot
+          if (fetch) {
+            const float4 q0 = __ldcs(rays + 2 * (size_t)r);
             const V3 o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
             const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
@@ -627,7 +632,6 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
     }
   }
 #undef RT_PUSH
-#undef RT_LEAF_TEST
   if (COUNT) {
     for (int o2 = 16; o2 > 0; o2 >>= 1) { n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o2); }
     if (lane == 0) { atomicAdd(stats, n_nodes); atomicAdd(stats + 1, n_leaves); }
@@ -639,3 +643,154 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
 #endif
   }
 }
+
+// ---- packet kernel: one warp walks the tree ONCE for 32 consecutive rays ----------------------------------
+// The queue order is pixel-major (render.cu, generate_kernel): 32 consecutive rays are the samples of one or two
+// pixels — the reference's own mapping, one warp = one pixel's 32 samples (draw.cu:135-213) — and the shadow rays
+// of their hits.  Such rays visit almost the same nodes, so the warp keeps ONE position and ONE stack (shared
+// memory, warp-uniform pushes and pops, no per-lane state machine, no refill logic) and every node and leaf record is
+// fetched once per warp: all lanes read the same address, one L1TEX wavefront instead of up to 32.
+//
+// Exactness.  The exact lane's answer is defined on leaves (see the top of this file): a ray's candidates are the
+// leaves whose OWN box passes the order-independent test and whose primitive test accepts, whatever the order of the
+// visits and whatever else is visited.  A lane therefore runs its own box tests (the same arithmetic as everywhere)
+// and takes part in a leaf test only when the leaf's box — a child half of the node just tested — passed for its own
+// ray and is not culled by its own key; an inner child is entered when ANY lane wants it.  A lane that did not want
+// a subtree is masked out below it (the mask travels with the stack entry).  Culling at pop time uses the smallest
+// key among the lanes that wanted the entry against the largest cut-off distance among the live lanes: skipped only
+// when every lane alone would have skipped it.  Near-first order is decided by majority.  Certificate, t2 and the
+// fallback list work per lane exactly as in traverse_near_kernel (any superset of tested candidates keeps the
+// argument: t2 only gets smaller).
+#ifndef RT_PKT_THREADS
+#define RT_PKT_THREADS 128
+#endif
+#ifndef RT_PKT_MIN_CTAS
+#define RT_PKT_MIN_CTAS 1
+#endif
+__device__ __forceinline__ unsigned rt_warp_min_u32(unsigned v) { return __reduce_min_sync(0xffffffffu, v); }
+__device__ __forceinline__ unsigned rt_warp_max_u32(unsigned v) { return __reduce_max_sync(0xffffffffu, v); }
+
+template <bool EXACT, bool COUNT, bool SUN>
+__global__ void __launch_bounds__(RT_PKT_THREADS, RT_PKT_MIN_CTAS) traverse_packet_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
+                                                                       const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
+                                                                       unsigned long long* stats, unsigned* __restrict__ fb_list,
+                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+  __shared__ unsigned s_range[2];
+  if (threadIdx.x == 0) { const unsigned nn = n_dev ? *n_dev : n_in; s_range[0] = nn; s_range[1] = (n_dev && cap_back) ? cap_back - nn : first_in; }
+  __syncthreads();
+  // warp-uniform stack entry: (reference, smallest culling key among the lanes that want it, their lane mask)
+  __shared__ uint4 s_stk[RT_PKT_THREADS / 32][RT_STACK_TOTAL];
+  uint4* const stk = s_stk[threadIdx.x >> 5];
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned n = s_range[0], first = s_range[1];
+  unsigned long long n_nodes = 0, n_leaves = 0, n_steps = 0;
+  const unsigned root = sc.n > 0 ? (unsigned)__ldg(sc.root) : 0u;
+  while (true) {
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(fetch_counter, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const unsigned r = first + base + lane;
+    bool valid = base + lane < n;
+    float4 q1 = make_float4(0.f, 0.f, 0.f, 0.f), q0 = q1;
+    if (valid) { q1 = __ldcs(rays + 2 * (size_t)r + 1); valid = __float_as_uint(q1.w) != RT_RAY_DEAD; }
+    if (valid) q0 = __ldcs(rays + 2 * (size_t)r);
+    const V3 d = mk3(q1.x, q1.y, q1.z);
+    const float tlimit = q0.w;
+    const RtRay2 q2 = rt_ray2(mk3(q0.x, q0.y, q0.z), mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z));  // bvh_traversal.cu:106
+    const float omk = (4e-7f * 1.000001f) * fmaxf(fmaxf(fabsf(q0.x), fabsf(q0.y)), fabsf(q0.z));
+    const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
+    unsigned fl = (anyhit ? F_ANYHIT : 0u) | ((!SUN && !(anyhit && tlimit == INFINITY)) ? F_WANTKEY : 0u);
+    float tmax = tlimit, tcull = tlimit, tcut = tlimit * 1.000001f, t2 = INFINITY;
+    int best = -1;
+    bool alive = valid;               // still searching
+    bool part = alive;                // wants the current node
+    unsigned cur = root; int sp = 0;
+    bool overflow = false;
+    // largest cut-off among the live lanes, as ordered bits (distances are >= 0): what a stack entry's key must not exceed
+    unsigned cutmax = SUN ? 0x7F800000u : rt_warp_max_u32(alive ? __float_as_uint(tcut) : 0u);
+    if (__ballot_sync(0xffffffffu, alive) != 0u && sc.n > 0) {
+      if (cur & RT_LEAF_BIT) {  // n == 1: the root is the leaf, tested without a box as in traverse_near_kernel
+        if (alive) { RT_LEAF_TEST(cur); }
+      } else
+      while (true) {
+        // ---- node step: both child boxes for every lane's own ray ----
+        if (COUNT) { n_nodes += part ? 1u : 0u; n_steps += lane == 0 ? 1u : 0u; }
+        const float4* np = sc.nodes + 4 * (size_t)cur;
+        float4 l0, l1, r0, r1;
+        rt_ld256(np, l0, l1); rt_ld256(np + 2, r0, r1);
+        float el, er; V3 tnl, tnr;
+        bool hl = rt_slab_tn2<true>(l0, l1, q2, (EXACT || SUN) ? INFINITY : tmax, el, tnl) && part;
+        bool hr = rt_slab_tn2<true>(r0, r1, q2, (EXACT || SUN) ? INFINITY : tmax, er, tnr) && part;
+        const unsigned refl = __float_as_uint(l1.z), refr = __float_as_uint(r1.z);
+        float kl = el, kr = er;
+        if (EXACT && !SUN) {
+          const V3 inv = rt_ray2_inv(q2);
+          kl = rt_key_inflated(tnl, l1.w, inv, omk); kr = rt_key_inflated(tnr, r1.w, inv, omk);
+          hl = hl && !(kl > tcut); hr = hr && !(kr > tcut);
+        }
+        const unsigned ml = __ballot_sync(0xffffffffu, hl), mr = __ballot_sync(0xffffffffu, hr);
+        // nearer child first, by majority of the lanes that hit anything
+        const unsigned vr = __ballot_sync(0xffffffffu, hr && (!hl || er < el));
+        const bool right_first = __popc(vr) > __popc((ml | mr) & ~vr);
+        // ---- leaf children: tested now, by the lanes whose own test passed the leaf's box ----
+        bool took = false;
+#pragma unroll 1
+        for (int k = 0; k < 2; k++) {
+          const bool isr = (k == 0) == right_first;
+          const unsigned ref = isr ? refr : refl, m = isr ? mr : ml;
+          if ((ref & RT_LEAF_BIT) && m) {  // warp-uniform
+            const bool h = isr ? hr : hl; const float key = isr ? kr : kl;
+            if (h && alive && !(EXACT && !SUN && key > tcut)) {
+              const int before = best; const float tbefore = tmax;
+              RT_LEAF_TEST(ref);
+              took = took || best != before || tmax != tbefore || (fl & F_FALLBACK);
+              if (((SUN || (fl & F_ANYHIT)) && best >= 0) || (fl & F_FALLBACK)) alive = false;
+            }
+          }
+        }
+        if (__ballot_sync(0xffffffffu, took)) {
+          if (__ballot_sync(0xffffffffu, alive) == 0u) break;  // every ray has its answer
+          if (!SUN) cutmax = rt_warp_max_u32(alive ? __float_as_uint(tcut) : 0u);
+        }
+        // ---- inner children ----
+        const bool il = !(refl & RT_LEAF_BIT) && ml, ir = !(refr & RT_LEAF_BIT) && mr;  // warp-uniform
+        bool pop = false;
+        if (il && ir) {
+          const unsigned refp = right_first ? refl : refr, mp = right_first ? ml : mr;
+          unsigned kp = 0u;
+          if (!SUN) kp = rt_warp_min_u32((right_first ? hl : hr) ? __float_as_uint(fmaxf(right_first ? kl : kr, 0.0f)) : 0x7F800000u);
+          if (sp < RT_STACK_TOTAL) { stk[sp] = make_uint4(refp, kp, mp, 0u); sp++; }
+          else overflow = true;  // the reference drops an entry here (bvh_traversal.cu:157-164): let its own order decide
+          cur = right_first ? refr : refl; part = (right_first ? hr : hl) && alive;
+        } else if (il) { cur = refl; part = hl && alive; }
+        else if (ir) { cur = refr; part = hr && alive; }
+        else pop = true;
+        if (pop) {
+          bool found = false;
+          while (sp > 0) {
+            sp--;
+            const uint4 e = stk[sp];
+            if (SUN || !(e.y > cutmax)) { cur = e.x; part = ((e.z >> lane) & 1u) != 0u && alive; found = true; break; }
+          }
+          if (!found) break;
+        }
+      }
+    }
+    if (valid) {
+      if (overflow) fl |= F_FALLBACK;
+      if (EXACT && ((fl & F_FALLBACK) || ((fl & F_INCONS) && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;
+      else {
+        const RtHit h = rt_finish_with_planes(sc, rt_ray2_o(q2), d, tlimit, SUN || (fl & F_ANYHIT), tmax, best);
+        __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+      }
+    }
+  }
+  if (COUNT) {
+    for (int o2 = 16; o2 > 0; o2 >>= 1) {
+      n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2); n_leaves += __shfl_xor_sync(0xffffffffu, n_leaves, o2); n_steps += __shfl_xor_sync(0xffffffffu, n_steps, o2);
+    }
+    if (lane == 0) { atomicAdd(stats, n_nodes); atomicAdd(stats + 1, n_leaves); atomicAdd(stats + 9, n_steps); }
+  }
+}
+#undef RT_LEAF_TEST

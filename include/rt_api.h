@@ -123,10 +123,18 @@ enum {
                                  that call touches the render's output buffers.  Same pixels either way.
                                  rt_scene_begin_frame moves the fork point earlier (e.g. before the caller's
                                  own vertex upload)                                                        */
-  RT_RENDER_SERIAL_PASSES = 128u /* one pass at a time on `stream` alone.  Default: two passes in flight on two
+  RT_RENDER_SERIAL_PASSES = 128u, /* one pass at a time on `stream` alone.  Default: two passes in flight on two
                                  streams with a state pool each, so that the drain of one pass's kernels (its
                                  longest rays) overlaps the other pass's work; traverse_ms then adds up launch
                                  durations that overlap each other.  Same pixels either way.               */
+  RT_TRAVERSE_PACKET  = 256u, /* near-first lanes: one warp walks the tree ONCE for 32 consecutive rays of the
+                                 queue (one position, one stack, every node fetched once per warp).  rt_render
+                                 does this by default where consecutive rays are coherent — primary rays (the
+                                 samples of a pixel are consecutive, the reference's one-warp-per-pixel mapping,
+                                 draw.cu:135-213) and, in scenes without mirrors, glass or GI, their shadow rays;
+                                 the flag forces it for every launch (rt_trace: the caller's rays).  Same hits:
+                                 the exact lane's answer does not depend on the visiting order */
+  RT_TRAVERSE_PER_RAY = 512u  /* never use the packet kernel: 32 independent rays per warp                  */
 };
 int rt_scene_begin_frame(rt_scene* scene, void* stream);
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
@@ -144,6 +152,8 @@ typedef struct rt_counters {
   float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS / RT_TIME_TRAVERSE) */
   uint32_t traverse_launches;
   uint64_t fallback_rays;   /* exact lane: rays re-traced in reference order (certificate failed)   */
+  uint64_t packet_steps;    /* node steps of the packet kernel, one per WARP step (RT_COUNTERS): nodes_visited /
+                               (32 * packet_steps) = share of the lanes that wanted the node a warp fetched  */
 } rt_counters;
 int rt_render(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
               uint8_t* d_rgba, int32_t* d_hit_id, uint8_t* d_written, rt_counters* counters, void* stream);

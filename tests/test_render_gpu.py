@@ -53,7 +53,7 @@ def check_trace(gi, gt, ids, ts, flags):
         assert np.array_equal(gt.view(np.uint32), ts.view(np.uint32)), "hit distances differ"
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER, api.TRAVERSE_PACKET, api.TRAVERSE_PACKET | api.TRAVERSE_NEAR_FIRST])
 @pytest.mark.parametrize("mode", [O.BOUNDS_COMPUTED, O.BOUNDS_SHIPPED])
 def test_trace_ids_mixed_scene(flags, mode):
     cfg, a = H.mixed_scene(3000)
@@ -68,7 +68,7 @@ def test_trace_ids_mixed_scene(flags, mode):
 
 
 @pytest.mark.parametrize("name", ["tri", "redchair", "tenthousand", "spiral"])
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER, api.TRAVERSE_PACKET])
 def test_trace_ids_scene_files(name, flags):
     p = H.scene_path(name)
     if p is None:
@@ -166,7 +166,7 @@ def synthetic_full_featured(n=4000, seed=11, rough=0.0):
     return cfg, a
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER, api.TRAVERSE_PACKET, api.TRAVERSE_PER_RAY])
 def test_render_all_shading_paths(flags):
     cfg, a = synthetic_full_featured()
     o = H.oracle_from_arrays(cfg, a)
@@ -482,3 +482,88 @@ def test_wide4_tree_gives_the_same_hits():
             print("steps per ray: binary %.2f, 4-wide %.2f" % (cb.nodes_visited / len(org), cw.nodes_visited / len(org)))
             assert cw.nodes_visited < 0.75 * cb.nodes_visited
         sc.close()
+
+
+def coherent_rays(groups, seed, spread=2e-3):
+    """bundles of 32 nearly identical rays (what a warp of the packet kernel gets from a pixel-major queue), plus
+    bundles whose rays fan out more and more, down to unrelated rays"""
+    rng = np.random.RandomState(seed)
+    org, d = random_rays(groups, seed, 2.5)
+    org = np.repeat(org, 32, axis=0); d = np.repeat(d, 32, axis=0)
+    s = np.repeat(spread * (4.0 ** rng.randint(0, 6, groups)), 32)[:, None].astype(np.float32)
+    org = (org + s * rng.uniform(-1, 1, org.shape)).astype(np.float32)
+    d = d + s * rng.uniform(-1, 1, d.shape).astype(np.float32)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return np.ascontiguousarray(org), np.ascontiguousarray(d)
+
+
+def test_packet_kernel_gives_the_reference_order_hits():
+    """traverse_packet_kernel (one warp walks the tree once for 32 consecutive rays): ids and distances bit-identical
+    to the reference-order lane for coherent bundles, fanned-out bundles and unrelated rays; triangles, spheres, the
+    mixed scene with duplicate codes and a plane, slivers (certificate + fallback at work), the redchair mesh, trees of
+    1, 2, 3 and 5 leaves, both bounds modes' trees (shipped: one code, a degenerate chain)."""
+    scenes = []
+    for gen in (synth.soup, synth.spheres):
+        cfg, a = gen(100_000, seed=2, width=160, height=120, aa=0)
+        scenes.append((H.oracle_from_arrays(cfg, synth.finish_triangles(a)), O.BOUNDS_COMPUTED))
+    cfg, a = H.mixed_scene(5000)
+    a["planes"] = np.array([[0, 1, 0, 1.2] + [0, 1, 0] + [0, -1.2, 0] + [0.5, 0.5, 0.5, 0, 0, 0, 0, 0, 0, 1.458, 0]], np.float32)
+    scenes.append((H.oracle_from_arrays(cfg, a), O.BOUNDS_COMPUTED))
+    cfg, a = H.mixed_scene(600)
+    scenes.append((H.oracle_from_arrays(cfg, a), O.BOUNDS_SHIPPED))
+    cfg, a = sliver_scene()
+    scenes.append((H.oracle_from_arrays(cfg, a), O.BOUNDS_COMPUTED))
+    for n in (1, 2, 3, 5):
+        cfg, a = synth.soup(n, seed=n, width=32, height=32, aa=0)
+        scenes.append((H.oracle_from_arrays(cfg, synth.finish_triangles(a)), O.BOUNDS_COMPUTED))
+    p = H.scene_path("redchair")
+    if p is not None:
+        scenes.append((O.OracleScene(p), O.BOUNDS_COMPUTED))
+    o1, d1 = coherent_rays(6000, 5)
+    o2, d2 = random_rays(100_003, 6, 2.0)   # not a multiple of 32: the last packet is ragged
+    org = np.concatenate([o1, o2]); d = np.concatenate([d1, d2])
+    for o, mode in scenes:
+        sc = built_pair(o, mode)
+        ri, rt_, _ = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER)
+        pi, pt, cp = gpu_trace(sc, org, d, api.TRAVERSE_PACKET | api.COUNTERS)
+        assert np.array_equal(pi, ri) and np.array_equal(pt.view(np.uint32), rt_.view(np.uint32)), "%d rays differ" % (pi != ri).sum()
+        if o.counts()["prims"] > 1000:
+            assert cp.packet_steps > 0
+            print("prims %d: lanes that wanted the node a warp fetched: %.1f of 32" % (o.counts()["prims"], cp.nodes_visited / cp.packet_steps))
+        ni, nt, _ = gpu_trace(sc, org, d, api.TRAVERSE_PACKET | api.TRAVERSE_NEAR_FIRST)
+        assert (ni != ri).mean() <= 1e-3
+        sc.close()
+
+
+def test_packet_and_per_ray_renders_are_identical(monkeypatch):
+    """rt_render's default (packet kernel where the queue is coherent), RT_TRAVERSE_PACKET (every launch),
+    RT_TRAVERSE_PER_RAY (never) and the reference-order lane give the same bytes, ids and ray counts: 1 spp and
+    multi-sample (pixel-major sample ids: 5, 16, 32 and 64 samples per pixel), sun + bulb shadow rays, mirrors + glass
+    + GI, interleaved tiles, many small passes, queued and host-driven schedules."""
+    cases = []
+    cfg, a = synth.soup(50_000, seed=3, width=200, height=120, aa=4)
+    o = H.oracle_from_arrays(cfg, synth.finish_triangles(a)); o.add_bulb((0.5, 0.8, 2.5), (3, 3, 3)); o.add_sun((-1, 2, 1), (0.5, 0.4, 0.3))
+    cases.append(o)
+    cfg, a = synthetic_full_featured(3000, 12)
+    cases.append(H.oracle_from_arrays(cfg, a))
+    cfg, a = sliver_scene(3000, 4)
+    cases.append(H.oracle_from_arrays(cfg, a))
+    for o in cases:
+        for aa, fl, (w, h), tiles in ((0, 0, (200, 120), None), (5, api.SPP_TRUE, (100, 60), None), (16, api.SPP_TRUE, (100, 60), api.TileSet(32, 8, 3, 1)),
+                                      (32, 0, (60, 40), None), (64, api.SPP_TRUE, (40, 30), None), (20, 0, (60, 40), None)):
+            ref = None
+            for pool, host_driven, lane in ((None, False, api.TRAVERSE_REF_ORDER), (None, False, 0), (None, False, api.TRAVERSE_PACKET), (None, False, api.TRAVERSE_PER_RAY),
+                                            (400_000, False, 0), (None, True, 0), (400_000, True, api.TRAVERSE_PACKET)):
+                if pool is None: monkeypatch.delenv("RT_POOL_BYTES", raising=False)
+                else: monkeypatch.setenv("RT_POOL_BYTES", str(pool))
+                if host_driven: monkeypatch.setenv("RT_HOST_DRIVEN", "1")
+                else: monkeypatch.delenv("RT_HOST_DRIVEN", raising=False)
+                sc = built_pair(o)
+                r = sc.render(w, h, aa, fl | lane, tiles=tiles, want_ids=True, want_written=True)
+                sc.close()
+                if ref is None:
+                    ref = r
+                    continue
+                assert np.array_equal(r["rgba"], ref["rgba"]), "image differs (aa %d, lane %d, pool %s): %d bytes" % (aa, lane, pool, (r["rgba"] != ref["rgba"]).sum())
+                assert np.array_equal(r["ids"], ref["ids"]) and np.array_equal(r["written"], ref["written"])
+                assert r["counters"].rays == ref["counters"].rays and r["counters"].samples == ref["counters"].samples
