@@ -1065,16 +1065,18 @@ int o_render(const o_scene* s, int W, int H, int aa, int spp_mode, int y0, int y
     covered = std::min<long long>(P, grid * 4);
   }
   skip_tables();
-  std::atomic<int> next(y0);
+  // work items of 16 consecutive pixels (not rows: a band of 4 rows would keep 4 threads busy and leave the rest idle)
+  const long long p_begin = (long long)y0 * W, p_end = (long long)y1 * W;
+  std::atomic<long long> next(p_begin);
   std::vector<o_counters> per((size_t)threads);
   for (auto& p : per) memset(&p, 0, sizeof(p));
   auto work = [&](int tid) {
     Ctx c(s);
     for (;;) {
-      int y = next.fetch_add(1);
-      if (y >= y1) break;
-      for (int x = 0; x < W; x++) {
-        int pix = y * W + x;
+      const long long b = next.fetch_add(16);
+      if (b >= p_end) break;
+      for (long long pp = b; pp < std::min(b + 16, p_end); pp++) {
+        int pix = (int)pp;
         if (pix >= covered) { if (written) written[pix] = 0; continue; }
         render_pixel(c, W, H, aa, spp_mode, pix, rgba_out + 4 * (size_t)pix, hit_id ? hit_id + pix : nullptr,
                      linear ? linear + 4 * (size_t)pix : nullptr);

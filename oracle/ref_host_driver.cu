@@ -186,14 +186,16 @@ void ref_render(ref_scene* r, int W, int H, int aa, int y0, int y1, int threads,
   const long long P = (long long)W * H;
   long long covered = P;
   if (aa >= 2) { long long grid = (P * aa + 127) / 128; covered = grid * 4 < P ? grid * 4 : P; }
-  std::atomic<int> next(y0);
+  // work items of 16 consecutive pixels (not rows: a band of 4 rows would keep 4 threads busy and leave the rest idle)
+  const long long p_begin = (long long)y0 * W, p_end = (long long)y1 * W;
+  std::atomic<long long> next(p_begin);
   auto work = [&]() {
     RawConfig local = cfg;
     for (;;) {
-      int y = next.fetch_add(1);
-      if (y >= y1) break;
-      for (int x = 0; x < W; x++) {
-        int pix = y * W + x;
+      const long long b = next.fetch_add(16);
+      if (b >= p_end) break;
+      for (long long pp = b; pp < (b + 16 < p_end ? b + 16 : p_end); pp++) {
+        int pix = (int)pp;
         if (pix >= covered) { if (written) written[pix] = 0; continue; }
         pixel_ref(&local, W, H, aa, pix, (pixel_t*)(rgba + 4 * (size_t)pix));
         if (written) written[pix] = 1;

@@ -29,6 +29,9 @@ RENDERS = [("tri", O.BOUNDS_SHIPPED, 100, 100, 0), ("tri", O.BOUNDS_COMPUTED, 10
            ("spiral", O.BOUNDS_COMPUTED, 32, 32, 0), ("spiral", O.BOUNDS_SHIPPED, 16, 16, 0)]
 
 
+FEATURE_RENDERS = [(48, 36, 0), (32, 24, 1), (16, 12, 32)]
+
+
 def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
@@ -66,6 +69,25 @@ def main():
         org, d = rays(4000, 11)
         ids, ts = r.trace_ids(org, d)
         out["trace"].append({"scene": name, "bounds": mode, "n": 4000, "seed": 11, "ids": sha(ids), "t": sha(ts), "hits": int((ids != -1).sum())})
+    # generated scene files for the branches no reference scene has: bulbs, fisheye, panorama, DOF on a soup, glass + bulb + GI
+    import tempfile
+    import feature_scenes as FS
+    out["feature"] = []
+    with tempfile.TemporaryDirectory() as tmp:
+        for kind in FS.KINDS:
+            p = FS.write(kind, os.path.join(tmp, kind + ".txt"))
+            o = O.OracleScene(p); b = o.build(O.BOUNDS_COMPUTED, 30)
+            r = R.RefScene(p); r.set_bvh(b)
+            a = r.arrays(); ints, fl = r.config()
+            e = {"kind": kind, "counts": r.n, "ints": ints, "floats_bits": fl.view(np.uint32).tolist(),
+                 "arrays": {k: (sha(v) if not isinstance(v, list) else [sha(x) for x in v]) for k, v in a.items()}, "render": []}
+            for W, H, aa in FEATURE_RENDERS:
+                rgba, wr = r.render(W, H, aa)
+                e["render"].append({"w": W, "h": H, "aa": aa, "rgba": sha(rgba), "written": int(wr.sum()), "nonzero_alpha": int((rgba[..., 3] > 0).sum())})
+            org, d = r.primary_rays(48, 36)
+            ids, ts = r.trace_ids(org, d)
+            e["primary"] = {"w": 48, "h": 36, "org": sha(org), "dir": sha(d), "ids": sha(ids), "t": sha(ts), "hits": int((ids != -1).sum())}
+            out["feature"].append(e)
     json.dump(out, open(os.path.join(HERE, "reference_host.json"), "w"), indent=1)
     print("wrote reference_host.json:", {k: len(v) for k, v in out.items()})
 

@@ -11,6 +11,7 @@ import sys
 import numpy as np
 import pytest
 
+import feature_scenes as FS
 import oracle_lib as O
 from cuda_ray_tracer_b200 import api, parallel, synth
 
@@ -42,7 +43,17 @@ def test_abi_struct_sizes_match_header():
 @pytest.mark.skipif(not have_scenes, reason="scene fixtures not present")
 @pytest.mark.parametrize("name", ["tri", "redchair", "tenthousand", "spiral"])
 def test_parser_matches_oracle(name):
-    path = os.path.join(O.SCENE_DIR, name + ".txt")
+    _check_parser_against_oracle(os.path.join(O.SCENE_DIR, name + ".txt"))
+
+
+@pytest.mark.parametrize("kind", FS.KINDS)
+def test_parser_matches_oracle_on_feature_scenes(kind, tmp_path):
+    """bulb / fisheye / panorama / dof / gi / expose / up / per-primitive shininess, transparency, ior, roughness lines
+    (tests/feature_scenes.py; the oracle's parse of the same files is pinned to parse.cpp in test_oracle_cpu.py)"""
+    _check_parser_against_oracle(FS.write(kind, str(tmp_path / (kind + ".txt"))))
+
+
+def _check_parser_against_oracle(path):
     hs = api.parse_scene_file(path); d = hs.desc
     o = O.OracleScene(path); c = o.config(); a = o.arrays(); n = o.counts()
     assert (d.width, d.height, d.bounces, d.aa, d.gi, d.fisheye, d.panorama) == (c["width"], c["height"], c["bounces"], c["aa"], c["gi"], int(c["fisheye"]), int(c["panorama"]))
