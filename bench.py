@@ -9,9 +9,10 @@ With N > 1 the scene is replicated, the image is split into interleaved 32x8 til
 and the framebuffer is summed onto rank 0 over NCCL inside the timed region: total work is fixed, so
 scaling is "strong".
 
-`--impl reference` times the reference's own traversal + shading sources compiled for the host
-(oracle/_ref/libref_host.so, all host threads) on a bounded sample of rows of the same frame; the fork has
-no CPU renderer and no way to run without CUDA, so this is its hot path on the box's host cores."""
+`--impl reference` times the reference's own CUDA program (oracle/_ref/ref_gpu_fast: unmodified kernels compiled
+for sm_100, the baseline BASELINE.json names) on the same GPU and scene, and carries the reference's traversal + shading
+sources compiled for the host (oracle/_ref/libref_host.so, all host threads, a bounded sample of rows) as its
+cpu_baseline leg; the fork has no CPU renderer of its own."""
 import argparse
 import json
 import os
@@ -116,61 +117,70 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------------
 def run_reference(a):
-    """reference arm: the reference's own hitNearest / shootPrimaryRay / curand path on the host cores"""
+    """Reference arm.  BASELINE.json names the baseline: "the reference's own CUDA build compiled unmodified for sm_100
+    in the same run" — the reference is a CUDA program with no CPU renderer.  So `value` is oracle/_ref/ref_gpu_fast
+    (the reference's unmodified kernels, nvcc -O3 defaults, sm_100; oracle/ref_gpu_driver.cu in place of main.cu) on
+    this box's GPU, one step = its build_lbvh_karas + render() of the same soup at the same image size; none of this
+    library's kernels run inside the timed steps.  The `cpu_baseline` leg is the reference's traversal + shading
+    sources compiled for the HOST (oracle/_ref/libref_host.so) on every host core, on a bounded sample of rows.
+    Without a GPU or without the prebuilt binary the CPU leg is the line's value."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import oracle_lib as O
-    import ref_lib as R
-    import helpers as H
     from cuda_ray_tracer_b200 import synth
-    kind = "reference" if R.available() else "port"
-    cores = os.cpu_count() or 1
     cfg, arrays = synth.soup(a.tris, 1, a.width, a.height, a.spp)
     p0, p1, p2 = frame_vertices(arrays, 0)
-    arrays["tri"] = [p0, p1, p2, None, None, None]
-    nor, e1, e2 = O.triangle_setup(p0, p1, p2)
-    arrays["tri"] = [p0, p1, p2, nor, e1, e2]
-    o = H.oracle_from_arrays(cfg, arrays)
-    t0 = time.time(); b = o.build(O.BOUNDS_COMPUTED, 30); build_s = time.time() - t0  # K1..K6 are __global__ code: CPU restatement
-    ref = None
-    if kind == "reference":
-        ref = R.scene_from_arrays(cfg, arrays); ref.set_bvh(b)
-    W, Hh, spp = a.width, a.height, a.spp
-    # the reference's render() runs 32 samples per pixel whenever aa >= 2 (SURVEY F3); a row of the image is
-    # W*32 primary samples there and W*spp here.  Sample = a band of rows through the middle of the image.
-    ref_spp = 32 if spp >= 2 else 1
-
-    def render_rows(y0, y1):
-        t = time.time()
-        if ref is not None:
-            ref.render(W, Hh, spp if spp < 2 else 32, y0, y1, cores)
+    host_arrays = {"tri_mat": arrays["tri_mat"], "refs": arrays["refs"], "suns": arrays["suns"]}
+    cpu = cpu_baseline(a, cfg, dict(host_arrays, tri=arrays["tri"][:3]))  # displaces the vertices to frame 0 itself
+    W, Hh = a.width, a.height
+    aa = 32 if a.spp >= 2 else a.spp
+    total = a.steps + a.warmup
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_fast")
+    gpu = None
+    try:
+        import torch
+        have_gpu = torch.cuda.is_available()
+    except Exception:
+        have_gpu = False
+    if have_gpu and os.path.exists(exe):
+        from cuda_ray_tracer_b200 import api
+        nor, e1, e2 = O.triangle_setup(p0, p1, p2)
+        arr = dict(host_arrays); arr["tri"] = [p0, p1, p2, nor, e1, e2]
+        path = "/tmp/bench_soup_%d.txt" % a.tris
+        synth.write_scene_text(path, cfg, arr, "bench_soup.png")
+        p = subprocess.run([exe, path, "--bounds", "computed", "--w", str(W), "--h", str(Hh), "--aa", str(aa), "--repeat", str(total)],
+                           capture_output=True, text=True, timeout=3000, cwd="/tmp")
+        if p.returncode == 0:
+            info = json.loads(p.stdout.strip().splitlines()[-1])
+            # the reference carries no ray counter; the ray count is a property of (scene, seed, sample semantics): counted once,
+            # outside the timed steps, by this library rendering the same file with the reference's sample semantics
+            hs = api.parse_scene_file(path)
+            mine = api.Scene(hs.desc, 0)
+            mine.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+            rays = mine.render(W, Hh, aa, 0)["counters"].rays
+            mine.close()
+            step_s = [r + b * 1e-3 for r, b in zip(info["render_s"], info["build_ms"])][a.warmup:]
+            gpu = {"value": rays / float(np.mean(step_s)) / 1e6, "ms_per_step": float(np.mean(step_s)) * 1e3, "rays_per_step": rays,
+                   "render_s": info["render_s"][a.warmup:], "build_ms": info["build_ms"][a.warmup:], "parse_s": info["parse_s"]}
         else:
-            o.render(W, Hh, spp if spp < 2 else 32, O.SPP_REF, y0, y1, cores)
-        return time.time() - t
-
-    def count_rays(y0, y1):  # the reference carries no ray counter: the oracle port counts hitNearest calls of the same rows
-        return o.render(W, Hh, spp if spp < 2 else 32, O.SPP_REF, y0, y1, cores)["counters"].rays
-
-    mid = Hh // 2
-    t_probe = render_rows(mid, mid + 1)
-    total_steps = a.steps + a.warmup
-    rows = max(1, min(Hh // 4, int(a.cpu_seconds * 16 / max(t_probe, 1e-3) / max(total_steps, 1))))
-    vals = []; secs = []
-    for s in range(total_steps):
-        y0 = max(0, min(Hh - rows, mid - rows // 2 + s)); y1 = y0 + rows
-        dt = render_rows(y0, y1)
-        rays = count_rays(y0, y1)
-        if s >= a.warmup:
-            vals.append(rays / dt / 1e6); secs.append(dt)
-    v = float(np.mean(vals))
+            gpu = {"error": (p.stdout[-300:] + p.stderr[-300:])}
+    if gpu is not None and "value" in gpu:
+        v = gpu["value"]; ms = gpu["ms_per_step"]; kind = "reference-cuda"
+        sample = ("the reference's CUDA program on this GPU: build_lbvh_karas + render() of soup frame 0 at %dx%d, aa=%d (it renders 32 samples per pixel "
+                  "whenever aa >= 2, SURVEY F3; Mrays/s = hitNearest calls of that frame / step time), scene bounds stored (as shipped every Morton code is 0)" % (W, Hh, aa))
+    else:
+        v = cpu["value"]; ms = None; kind = cpu["kind"]; sample = cpu["sample"]
     line = {"metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": float(np.mean(secs)) * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "impl": "reference",
-            "config": {"workload": workload_name(a), "sample": "%d rows of the frame at %d spp per step" % (rows, ref_spp)},
-            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind,
-                             "sample": "%d image rows x %d px x %d spp per step (reference render() semantics), BVH from the CPU restatement of K1..K6 (%.2f s, 1 core)" % (rows, W, ref_spp, build_s)},
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "reference", "reference_kind": kind,
+            "config": {"workload": workload_name(a), "reference_arm": sample},
+            "cpu_baseline": cpu,
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if gpu is not None:
+        line["reference_cuda"] = gpu
+        if "build_ms" in gpu:
+            line["lbvh_build_ms"] = float(np.mean(gpu["build_ms"]))
     print(json.dumps(line))
 
 
@@ -247,6 +257,23 @@ def gpu_baseline(a, sc, cfg, arrays, api, synth):
             "reference_mrays_s": rays / min(info["render_s"]) / 1e6, "reference_render_s": min(info["render_s"]),
             "reference_build_ms": min(info["build_ms"]), "reference_parse_s": info["parse_s"],
             "b200_mrays_s": rays / best / 1e3, "b200_render_s": best * 1e-3, "host_cores": os.cpu_count()}
+
+
+def measure_l2_peaks():
+    """L2 ceilings of this GPU for the traversal kernel's access shapes, measured in this run by scripts/microbench/l2bw
+    (built by __graft_entry__.build(); 64 MB L2-resident array, all SMs): a coalesced stream of 32-byte loads, 64-byte
+    records at random indices with one record per lane, and the same with lane pairs sharing a record's line."""
+    exe = os.path.join(ROOT, "scripts", "microbench", "l2bw")
+    if not os.path.exists(exe):
+        return {"unavailable": "scripts/microbench/l2bw is not built"}
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout
+        import re
+        g = lambda pat: float(re.search(pat + r"[^:]*:\s*([0-9.]+) GB/s", out).group(1))
+        return {"l2_stream_gbs": g("L2 stream"), "l2_gather64_gbs": g("L2 gather, 64-byte records at random"),
+                "l2_gather64_pair_shfl_gbs": g(r"lane pairs \+ 8 shuffles"), "hbm_gather64_gbs": g("HBM gather"), "how": "scripts/microbench/l2bw, this run"}
+    except Exception as e:
+        return {"unavailable": repr(e)}
 
 
 def run_b200(a):
@@ -400,10 +427,11 @@ def run_b200(a):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic = None  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this command
+    traffic = None; traffic_src = None  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this command
     try:
-        prof = "ncu_traverse_r01.json" if a.tris == 1_000_000 else "ncu_traverse_%dm_r01.json" % (a.tris // 1_000_000)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", prof)))["dram_bytes_per_launch_mean"]
+        prof = "ncu_traverse_r02.json" if a.tris == 1_000_000 else "ncu_traverse_%dm_r02.json" % (a.tris // 1_000_000)
+        pj = json.load(open(os.path.join(ROOT, "profiles", prof)))
+        traffic = pj["dram_bytes_per_launch_mean"]; traffic_src = "profiles/%s (captured at commit %s)" % (prof, pj.get("commit", "?"))
     except Exception:
         pass
     # per-launch figures: algorithmic bytes of one frame / traverse launches of one frame; duration = live CUDA-event average
@@ -411,11 +439,7 @@ def run_b200(a):
     bytes_per_launch = alg[0].item() / world / max(launches_per_frame, 1)   # per rank, like the per-rank event time
     ms_per_launch = ser_res["trav_ms"] / max(ser_res["trav_launches"], 1)
     achieved = bytes_per_launch / (ms_per_launch * 1e-3) / 1e9 if ms_per_launch > 0 else 0.0
-    l2 = {}
-    try:
-        l2 = json.load(open(os.path.join(ROOT, "profiles", "l2_peaks_r01.json")))
-    except Exception:
-        pass
+    l2 = measure_l2_peaks()  # after the timed loops: same GPU, same run
     value = dev_res["rays"] / (dev_res["ms"] * 1e-3) / 1e6
     e2e = e2e_res["rays"] / (e2e_res["ms"] * 1e-3) / 1e6
     line = {
@@ -436,16 +460,18 @@ def run_b200(a):
         "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 3 * 12 * n, "d2h_bytes_per_step": W * Hh * 4,
                 "ms_per_step": e2e_res["ms"] / a.steps},
         "gpu_launches": int(dev_res["launches"]),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_note": ("dram__bytes_read+write per launch, mean of the 4 launches in profiles/ncu_traverse_r01.json: the ray records in and the hits out; node and leaf fetches hit in L2"
-                                      if a.tris == 1_000_000 else "dram__bytes_read+write per launch, mean of the launches in profiles/ncu_traverse_%dm_r01.json (null when that capture does not exist)" % (a.tris // 1_000_000)),
-                     "kernel": "traverse_near_kernel<EXACT=%d>" % (0 if a.near_first else 1), "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+        "roofline": {"bound": "l2", "achieved": achieved, "peak": l2.get("l2_stream_gbs"), "unit": "GB/s",
+                     "frac": (achieved / l2["l2_stream_gbs"]) if l2.get("l2_stream_gbs") else None,
+                     "traffic": traffic, "traffic_source": traffic_src,
+                     "kernel": "traverse_near_kernel<EXACT=%d>" % (0 if a.near_first else 1),
+                     "peak_source": "L2 stream rate of a 64 MB resident array, measured in this run (scripts/microbench/l2bw); MEASURED_PEAKS.json has no L2 figure",
                      "bytes_per_launch": bytes_per_launch, "ms_per_launch": ms_per_launch,
                      "share_of_step": ser_res["trav_ms"] / ser_res["ms"],
                      "timed_how": "CUDA events around every traverse launch of %d frames rendered one pass at a time (RT_RENDER_SERIAL_PASSES), %.2f ms per frame; the headline frames keep two passes in flight, where a launch interval would include waiting for the other pass" % (a.steps, ser_res["ms"] / a.steps),
-                     "l2_gather_peak": l2.get("l2_gather64_gbs"), "frac_of_l2_gather": (achieved / l2["l2_gather64_gbs"]) if l2.get("l2_gather64_gbs") else None,
-                     "l2_gather_pair_peak": l2.get("l2_gather64_pair_shfl_gbs"), "frac_of_l2_gather_pair": (achieved / l2["l2_gather64_pair_shfl_gbs"]) if l2.get("l2_gather64_pair_shfl_gbs") else None,
-                     "note": "algorithmic bytes = 64 B per internal node visited + 48 B per triangle test. The 64 MB of nodes and 96 MB of leaf records are served by L2 (92-96 % hit rate, DRAM traffic = rays in + hits out), so the rate can exceed the HBM copy peak; the bound that applies is the measured L2 rate for 64-byte random gathers (profiles/l2_peaks_r01.json, BASELINE.json's 'traversal roofline ... against L2 bandwidth'): l2_gather_peak with one load per lane (what the kernel does), l2_gather_pair_peak when lane pairs share each record's 128-byte line (half the L1TEX wavefronts; the same fetch inside the kernel lost 18-25 % to its shuffles and registers, DESIGN.md 4.2)"},
+                     "hbm_peak": peak, "frac_hbm": achieved / peak, "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                     "l2_gather_peak": l2.get("l2_gather64_gbs"), "frac_l2_gather": (achieved / l2["l2_gather64_gbs"]) if l2.get("l2_gather64_gbs") else None,
+                     "l2_gather_pair_peak": l2.get("l2_gather64_pair_shfl_gbs"), "l2_measured": l2,
+                     "note": "algorithmic bytes = 64 B per internal node a ray visits + 48 B per triangle test (SURVEY 8d), counted by an instrumented frame. The 64 MB of nodes and 96 MB of leaf records are served by L1 and L2 (DRAM traffic = the ray records in and the hits out, `traffic`), so the bound is the L2 and `frac` is against its measured stream rate; frac_hbm is kept for the record and exceeds 1 because HBM is not what feeds the kernel. l2_gather_peak is what 32 lanes reading 32 unrelated 64-byte records reach from L2 (one L1TEX wavefront per lane per 32-byte load): the pixel-major queue order lets the kernel EXCEED it, because lanes of a warp that trace samples of the same pixel read the same lines (one wavefront for several lanes, L1 hits)"},
         "clocks": sampler.summary() if sampler is not None else None,
     }
     if diag:

@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libb200rt.so")  # RT
 
 BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN, BUILD_LOCAL_CLIMB, BUILD_WIDE4 = 0, 1, 2, 4, 8
 SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE, TRAVERSE_REF_ORDER, RENDER_OVERLAP_BUILD, RENDER_SERIAL_PASSES = 0, 1, 2, 4, 8, 16, 32, 64, 128
-TRAVERSE_PACKET, TRAVERSE_PER_RAY = 256, 512
+TRAVERSE_PACKET = 256
 
 
 class RtError(RuntimeError):
@@ -62,7 +62,10 @@ _lib = None
 EXPORTS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_update_triangles", "rt_build_lbvh", "rt_scene_build_ms", "rt_scene_begin_frame", "rt_render", "rt_render_host",
            "rt_trace", "rt_export_reference_layout", "rt_scene_num_prims", "rt_parse_scene_file", "rt_host_scene_desc",
            "rt_host_scene_filename", "rt_host_scene_bounds", "rt_host_scene_free", "rt_triangle_setup", "rt_png_write",
-           "rt_png_read", "rt_free", "rt_xorwow_init", "rt_last_error", "rt_version"]
+           "rt_png_read", "rt_free", "rt_xorwow_init", "rt_last_error", "rt_version",
+           "rt_comm_init", "rt_comm_unique_id", "rt_comm_init_rank", "rt_comm_destroy", "rt_comm_size", "rt_comm_num_local", "rt_comm_local_rank",
+           "rt_comm_local_device", "rt_tile_shape", "rt_scene_broadcast", "rt_comm_update_triangles", "rt_comm_build_lbvh", "rt_framebuffer_gather",
+           "rt_render_multi", "rt_render_reserve", "rt_device_alloc", "rt_device_free"]
 
 
 def load_library():
@@ -98,6 +101,23 @@ def load_library():
     L.rt_png_read.argtypes = [C.c_char_p, C.POINTER(ip), C.POINTER(ip), C.POINTER(vp)]
     L.rt_free.argtypes = [vp]
     L.rt_xorwow_init.argtypes = [C.c_uint64, C.c_uint64, vp]
+    pvp = C.POINTER(vp)
+    L.rt_comm_init.argtypes = [ip, C.POINTER(ip), pvp]
+    L.rt_comm_unique_id.argtypes = [vp]
+    L.rt_comm_init_rank.argtypes = [ip, ip, vp, ip, pvp]
+    L.rt_comm_destroy.argtypes = [vp]
+    for n in ("rt_comm_size", "rt_comm_num_local"):
+        getattr(L, n).argtypes = [vp]
+    L.rt_comm_local_rank.argtypes = [vp, ip]; L.rt_comm_local_device.argtypes = [vp, ip]
+    L.rt_tile_shape.argtypes = [ip, ip, C.POINTER(ip), C.POINTER(ip)]; L.rt_tile_shape.restype = None
+    L.rt_scene_broadcast.argtypes = [vp, C.POINTER(SceneDesc), ip, pvp]
+    L.rt_comm_update_triangles.argtypes = [vp, pvp, vp, vp, vp, ip, pvp]
+    L.rt_comm_build_lbvh.argtypes = [vp, pvp, ip, C.c_uint, C.POINTER(C.c_float)]
+    L.rt_framebuffer_gather.argtypes = [vp, pvp, ip, ip, ip, ip, ip, pvp]
+    L.rt_render_reserve.argtypes = [vp, ip, ip]
+    L.rt_device_alloc.argtypes = [ip, C.c_size_t]; L.rt_device_alloc.restype = vp
+    L.rt_device_free.argtypes = [ip, vp]; L.rt_device_free.restype = None
+    L.rt_render_multi.argtypes = [vp, pvp, ip, ip, ip, C.c_uint, ip, ip, ip, pvp, vp, C.POINTER(Counters)]
     _lib = L
     return L
 
@@ -194,11 +214,14 @@ def parse_scene_file(path):
 class Scene:
     """Device-resident scene (RawConfig + its device arrays, include/config.hpp:75-126)."""
 
-    def __init__(self, desc, device=0, keepalive=None):
+    def __init__(self, desc, device=0, keepalive=None, handle=None):
         L = load_library()
         self.h = C.c_void_p()
         self.desc = desc
-        _check(L.rt_scene_create(C.byref(desc), device, C.byref(self.h)), "rt_scene_create")
+        if handle is not None:   # an rt_scene created by rt_scene_broadcast
+            self.h = C.c_void_p(handle)
+        else:
+            _check(L.rt_scene_create(C.byref(desc), device, C.byref(self.h)), "rt_scene_create")
         self.n = L.rt_scene_num_prims(self.h)
         self.device = device
 
@@ -295,3 +318,76 @@ def xorwow_init(seed, subsequence):
     st = np.zeros(6, np.uint32)
     load_library().rt_xorwow_init(seed, subsequence, _ptr(st))
     return st
+
+
+class Comm:
+    """rt_comm: one NCCL communicator over the GPUs that render one image (include/rt_api.h, csrc/comm.cu).
+    Comm(ndev=N): this process drives N GPUs.  Comm.from_torch_distributed(device): one process per GPU (torchrun),
+    the 128-byte NCCL id travels through torch.distributed."""
+
+    def __init__(self, ndev=None, devices=None, handle=None):
+        L = load_library()
+        self.h = C.c_void_p()
+        if handle is not None:
+            self.h = handle
+        else:
+            dv = (C.c_int * ndev)(*devices) if devices is not None else None
+            _check(L.rt_comm_init(ndev, dv, C.byref(self.h)), "rt_comm_init")
+        self.size = L.rt_comm_size(self.h); self.num_local = L.rt_comm_num_local(self.h)
+        self.ranks = [L.rt_comm_local_rank(self.h, k) for k in range(self.num_local)]
+        self.devices = [L.rt_comm_local_device(self.h, k) for k in range(self.num_local)]
+
+    @classmethod
+    def from_torch_distributed(cls, device):
+        import torch
+        import torch.distributed as dist
+        L = load_library()
+        rank, world = dist.get_rank(), dist.get_world_size()
+        idb = np.zeros(128, np.uint8)
+        if rank == 0:
+            _check(L.rt_comm_unique_id(_ptr(idb)), "rt_comm_unique_id")
+        t = torch.from_numpy(idb)
+        if dist.get_backend() == "nccl":
+            t = t.cuda(device); dist.broadcast(t, 0); idb = t.cpu().numpy()
+        else:
+            dist.broadcast(t, 0)
+        h = C.c_void_p()
+        _check(L.rt_comm_init_rank(world, rank, _ptr(np.ascontiguousarray(idb)), device, C.byref(h)), "rt_comm_init_rank")
+        return cls(handle=h)
+
+    def close(self):
+        if self.h:
+            load_library().rt_comm_destroy(self.h); self.h = C.c_void_p()
+
+    def _arr(self, items):
+        return (C.c_void_p * self.num_local)(*[(x.h if isinstance(x, Scene) else _ptr(x)) for x in items])
+
+    def broadcast_scene(self, desc, root=0):
+        """rt_scene_broadcast: desc on the root's process (None elsewhere) -> one Scene per local GPU"""
+        out = (C.c_void_p * self.num_local)()
+        _check(load_library().rt_scene_broadcast(self.h, C.byref(desc) if desc is not None else None, root, out), "rt_scene_broadcast")
+        return [Scene(desc, self.devices[k], handle=out[k]) for k in range(self.num_local)]
+
+    def update_triangles(self, scenes, p0, p1, p2, root=0):
+        _check(load_library().rt_comm_update_triangles(self.h, self._arr(scenes), _ptr(p0), _ptr(p1), _ptr(p2), root, None), "rt_comm_update_triangles")
+
+    def build_lbvh(self, scenes, bits=30, flags=BOUNDS_COMPUTED):
+        ms = C.c_float()
+        _check(load_library().rt_comm_build_lbvh(self.h, self._arr(scenes), bits, flags, C.byref(ms)), "rt_comm_build_lbvh")
+        return ms.value
+
+    def gather_framebuffer(self, images, w, h, tile_w, tile_h, root=0):
+        """images: one device image (torch tensor / pointer) per local GPU"""
+        _check(load_library().rt_framebuffer_gather(self.h, self._arr(images), w, h, tile_w, tile_h, root, None), "rt_framebuffer_gather")
+
+    def render(self, scenes, w, h, aa, images, flags=SPP_REF, tile_w=0, tile_h=0, root=0, host_out=None):
+        cnt = Counters()
+        _check(load_library().rt_render_multi(self.h, self._arr(scenes), w, h, aa, flags, tile_w, tile_h, root, self._arr(images), _ptr(host_out),
+                                              C.byref(cnt)), "rt_render_multi")
+        return cnt
+
+
+def tile_shape(ranks, width):
+    tw, th = C.c_int(), C.c_int()
+    load_library().rt_tile_shape(ranks, width if width else 0, C.byref(tw), C.byref(th))
+    return tw.value, th.value

@@ -55,8 +55,14 @@ __device__ inline RtBox rt_prim_box(float4 a, float4 b, float4 c) {
 // only when no acceptable hit inside the subtree can be closer — see traverse.cuh, exact near-first lane.
 // Evaluated in double from the float e1/e2 actually used by the test, so slivers with inaccurate
 // e1/e2 get the (large) slack they need; anything non-finite or ill-conditioned gets +INF (never culled).
+// sphere: 2e-3 r for the cancellation in sqrt(r^2 - d^2) away from the silhouette, plus 2e-6 per unit of |c| + r for a
+// small sphere far from the origin, where the rounding of c - o and t*d + o - c no longer hides inside 2e-3 r
+// (traverse.cuh, RT_ORIGIN_SLACK carries the ray-origin share of the same bound)
+__device__ inline float rt_sphere_slack(float4 a) {
+  return 2e-3f * fabsf(a.w) + 2e-6f * (fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fabsf(a.z)) + fabsf(a.w));
+}
 __device__ inline float rt_leaf_slack(float4 a, float4 b, float4 c, float4 t0, float4 t1, float4 t2, const RtBox& box) {
-  if (c.w == RT_TAG_SPHERE) return 2e-3f * fabsf(a.w);
+  if (c.w == RT_TAG_SPHERE) return rt_sphere_slack(a);
   const double p0[3] = {a.x, a.y, a.z}, p1[3] = {a.w, b.x, b.y}, p2[3] = {b.z, b.w, c.x};
   const double nor[3] = {t0.w, t1.x, t1.y}, e1[3] = {t1.z, t1.w, t2.x}, e2[3] = {t2.y, t2.z, t2.w};
   if (nor[0] == 0.0 && nor[1] == 0.0 && nor[2] == 0.0) return 0.f;  // den == 0 for every ray: never hit

@@ -1010,8 +1010,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;
   const bool time_trav = (flags & (RT_COUNTERS | RT_TIME_TRAVERSE)) != 0;
-  // packet traversal: 0 never, 1 coherent queues (primary rays; every ray of a scene without mirrors, glass or GI), 2 always
-  int pkt_mode = (flags & RT_TRAVERSE_PER_RAY) ? 0 : (flags & RT_TRAVERSE_PACKET) ? 2 : 1;
+  // packet traversal (opt-in, RT_TRAVERSE_PACKET): 0 never, 1 coherent queues (primary rays; every ray of a scene without
+  // mirrors, glass or GI), 2 every launch.  Measured on the 4K soup frame (profiles/packet_kernel_r02.json): only 17 of 32
+  // lanes want the node their warp fetches, 3300 Mrays/s against 4159 with independent lanes over the same pixel-major queue.
+  int pkt_mode = (flags & RT_TRAVERSE_PACKET) ? 2 : 0;
   if (const char* e = getenv("RT_PACKET")) pkt_mode = atoi(e);  // experiments
   const bool both = s->any_shiny && s->any_trans;
   const int gi = s->cfg.gi != 0 ? 1 : 0;
@@ -1322,10 +1324,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   return RT_OK;
 }
 
-extern "C" int rt_render_host(rt_scene* s, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles, uint8_t* h_rgba, int32_t* h_hit_id,
-                              uint8_t* h_written, rt_counters* counters) {
-  if (!s || !h_rgba) { rt_set_error("rt_render_host: null argument"); return RT_ERR_INVALID; }
-  if (w <= 0 || h <= 0) { rt_set_error("rt_render_host: bad image size"); return RT_ERR_INVALID; }
+// the device image rt_render_host renders into (the reference's cudaMalloc of d_image, main.cu:56-58), allocated ahead of
+// the first frame so that the frame's wall time holds no allocation
+extern "C" int rt_render_reserve(rt_scene* s, int w, int h) {
+  if (!s || w <= 0 || h <= 0) { rt_set_error("rt_render_reserve: bad argument"); return RT_ERR_INVALID; }
   RT_CUDA(cudaSetDevice(s->device));
   RenderState* rs = get_state(s);
   const size_t npx = (size_t)w * h;
@@ -1335,7 +1337,18 @@ extern "C" int rt_render_host(rt_scene* s, int w, int h, int aa, unsigned flags,
     RT_CUDA(cudaMalloc(&rs->d_rgba, npx * 4)); RT_CUDA(cudaMalloc(&rs->d_ids, npx * 4)); RT_CUDA(cudaMalloc(&rs->d_written, npx));
     rs->img_px = npx;
   }
-  const int rc = rt_render(s, w, h, aa, flags, tiles, rs->d_rgba, h_hit_id ? rs->d_ids : nullptr, h_written ? rs->d_written : nullptr, counters, nullptr);
+  return RT_OK;
+}
+
+extern "C" int rt_render_host(rt_scene* s, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles, uint8_t* h_rgba, int32_t* h_hit_id,
+                              uint8_t* h_written, rt_counters* counters) {
+  if (!s || !h_rgba) { rt_set_error("rt_render_host: null argument"); return RT_ERR_INVALID; }
+  if (w <= 0 || h <= 0) { rt_set_error("rt_render_host: bad image size"); return RT_ERR_INVALID; }
+  int rc = rt_render_reserve(s, w, h);
+  if (rc) return rc;
+  RenderState* rs = get_state(s);
+  const size_t npx = (size_t)w * h;
+  rc = rt_render(s, w, h, aa, flags, tiles, rs->d_rgba, h_hit_id ? rs->d_ids : nullptr, h_written ? rs->d_written : nullptr, counters, nullptr);
   if (rc) return rc;
   RT_CUDA(cudaMemcpy(h_rgba, rs->d_rgba, npx * 4, cudaMemcpyDeviceToHost));  // main.cu:77
   if (h_hit_id) RT_CUDA(cudaMemcpy(h_hit_id, rs->d_ids, npx * 4, cudaMemcpyDeviceToHost));

@@ -32,7 +32,7 @@ __global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* ma
     float rad = a.sr[r.y];
     bv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
     bv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-    bv[3 * (size_t)i + 2] = make_float4(0.f, 2e-3f * fabsf(rad), 0.f, RT_TAG_SPHERE);  // .y = hit slack (build.cuh)
+    bv[3 * (size_t)i + 2] = make_float4(0.f, rt_sphere_slack(make_float4(c[0], c[1], c[2], rad)), 0.f, RT_TAG_SPHERE);  // .y = hit slack (build.cuh)
     tv[3 * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
     tv[3 * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     tv[3 * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);

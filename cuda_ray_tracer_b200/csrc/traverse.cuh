@@ -164,8 +164,14 @@ __device__ __forceinline__ bool rt_prim_test(const float4* __restrict__ tv, cons
 
 // Lower bound of the entry distance of the node half's box inflated by S = aux + omk on every side, where aux
 // (node half word 7, written by the build) = hit slack of the subtree + 4e-7 * largest |coordinate| of the box
-// and omk = 4e-7 * largest |coordinate| of the ray origin: the slack covers accepted hits outside the box, the
-// 4e-7 terms the rounding of t*d + o inside the primitive test.
+// and omk = RT_ORIGIN_SLACK * largest |coordinate| of the ray origin: the slack covers accepted hits outside the box,
+// the coordinate terms the rounding of t*d + o inside the primitive test (4e-7 per unit of coordinate for the triangle
+// test).  The sphere test needs more from the origin term: t = tc - sqrt(r^2 - d^2) with c - o, tc and d^2 rounded at the
+// magnitude M = max(|o|, |c|) puts the accepted point up to ~(6 eps M + eta^2 / r) / 2 <= 1e-6 M outside the sphere's box
+// even at grazing incidence (the error of t itself is first order there, sqrt(6 eps r M), but it moves the point ALONG
+// a tangent, which leaves the box only in second order), whatever r is.  Hence 2e-6 per unit of |o| here and 2e-6 per
+// unit of |c| + r in the sphere's own slack (scene.cu); at |o| = 3.5 that inflates every box by 7e-6.
+#define RT_ORIGIN_SLACK 2e-6f
 // Per axis the inflated slab is entered at tn - S/|d| in real arithmetic.  tn (the exact test's own near
 // distance, fl(fl(b - o) * inv)) carries a relative error of at most 3 ulp, inv = fl(1/d) half an ulp, so
 // key = fma(-S * 1.000001, |inv|, tn) (the factor is folded into the stored aux and into omk) satisfies key <= t * (1 + 3e-7) for every accepted hit t of the subtree;
@@ -454,7 +460,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
             const V3 o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
             const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
-            omk = (4e-7f * 1.000001f) * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+            omk = (RT_ORIGIN_SLACK * 1.000001f) * fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
             q2 = rt_ray2(o, inv);
             tmax = tlimit; tcull = tlimit; tcut = tlimit * 1.000001f; t2 = INFINITY; best = -1; sp = 0; cur = sc.n > 0 ? (unsigned)__ldg(sc.root) : 0u;
             // a sun ray never culls by distance (tcull stays +INF) and needs no certificate
@@ -698,7 +704,7 @@ __global__ void __launch_bounds__(RT_PKT_THREADS, RT_PKT_MIN_CTAS) traverse_pack
     const V3 d = mk3(q1.x, q1.y, q1.z);
     const float tlimit = q0.w;
     const RtRay2 q2 = rt_ray2(mk3(q0.x, q0.y, q0.z), mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z));  // bvh_traversal.cu:106
-    const float omk = (4e-7f * 1.000001f) * fmaxf(fmaxf(fabsf(q0.x), fabsf(q0.y)), fabsf(q0.z));
+    const float omk = (RT_ORIGIN_SLACK * 1.000001f) * fmaxf(fmaxf(fabsf(q0.x), fabsf(q0.y)), fabsf(q0.z));
     const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
     unsigned fl = (anyhit ? F_ANYHIT : 0u) | ((!SUN && !(anyhit && tlimit == INFINITY)) ? F_WANTKEY : 0u);
     float tmax = tlimit, tcull = tlimit, tcut = tlimit * 1.000001f, t2 = INFINITY;

@@ -8,22 +8,11 @@ TILE_W, TILE_H = 32, 8
 
 
 def tile_shape(world, width=None):
-    """256-pixel tile shape for `world` ranks.  Tile t (row-major) belongs to rank t % world, so when the number of
-    tiles per image row is a multiple of world every rank would own whole COLUMNS of tiles and the load would
-    follow the picture's horizontal structure (measured: 7 % spread at 8 GPUs on the 4K soup).  Pick the shape
-    whose tiles-per-row shares the fewest factors with world (ties: the squarest), e.g. 256x1 at 3840 wide:
-    15 tiles per row, rank = (tx - ty) mod 8, a diagonal pattern."""
+    """256-pixel tile shape for `world` ranks: rt_tile_shape (csrc/comm.cu) — the shape whose tiles-per-row shares the
+    fewest factors with world, so that no rank owns whole columns of tiles (256x1 at 3840 wide: a diagonal pattern)."""
     if width is None or world <= 1:
         return TILE_W, TILE_H
-    import math
-    best = None
-    for tw, th in ((32, 8), (64, 4), (16, 16), (128, 2), (256, 1)):
-        tx = (width + tw - 1) // tw
-        waste = tx * tw - width
-        key = (math.gcd(tx, world), waste, abs(math.log2(tw / th)))
-        if best is None or key < best[0]:
-            best = (key, (tw, th))
-    return best[1]
+    return api.tile_shape(world, width)
 
 
 def tile_set(world, rank, tile_w=None, tile_h=None, width=None):
@@ -66,10 +55,30 @@ def upload_sharded(host_pinned, dev_full, dev_part, rank, world):
     return dev_full
 
 
-def gather_framebuffer(img, dst=0):
-    """sum the per-rank images onto rank `dst`: every rank wrote only its own tiles into a zeroed image, so the
-    sum over uint8 is the gather (33 MB at 4K: tens of microseconds over NVLink)"""
+_comm = None
+
+
+def comm(device=None):
+    """the process's rt_comm over torch.distributed's ranks (one GPU per process), created on first use"""
+    global _comm
+    if _comm is None:
+        import torch
+        _comm = api.Comm.from_torch_distributed(torch.cuda.current_device() if device is None else device)
+    return _comm
+
+
+def gather_framebuffer(img, dst=0, width=None, height=None, tile_w=None, tile_h=None):
+    """Every rank rendered only its own tiles into a zeroed image; afterwards rank `dst` holds the whole image.
+    CUDA tensors: rt_framebuffer_gather (each rank packs its tiles and sends 1/world of the image over NCCL).
+    Host tensors (the gloo tests of the partition logic): the sum over uint8 is the gather."""
     import torch.distributed as dist
-    if dist.is_initialized() and dist.get_world_size() > 1:
+    if not (dist.is_initialized() and dist.get_world_size() > 1):
+        return img
+    if img.is_cuda:
+        h, w = (img.shape[0], img.shape[1]) if height is None else (height, width)
+        if tile_w is None or tile_h is None:
+            tile_w, tile_h = tile_shape(dist.get_world_size(), w)
+        comm(img.device.index).gather_framebuffer([img], w, h, tile_w, tile_h, dst)
+    else:
         dist.reduce(img, dst, op=dist.ReduceOp.SUM)
     return img

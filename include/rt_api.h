@@ -10,6 +10,7 @@
  */
 #ifndef RT_API_H
 #define RT_API_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -127,14 +128,13 @@ enum {
                                  streams with a state pool each, so that the drain of one pass's kernels (its
                                  longest rays) overlaps the other pass's work; traverse_ms then adds up launch
                                  durations that overlap each other.  Same pixels either way.               */
-  RT_TRAVERSE_PACKET  = 256u, /* near-first lanes: one warp walks the tree ONCE for 32 consecutive rays of the
-                                 queue (one position, one stack, every node fetched once per warp).  rt_render
-                                 does this by default where consecutive rays are coherent — primary rays (the
-                                 samples of a pixel are consecutive, the reference's one-warp-per-pixel mapping,
-                                 draw.cu:135-213) and, in scenes without mirrors, glass or GI, their shadow rays;
-                                 the flag forces it for every launch (rt_trace: the caller's rays).  Same hits:
-                                 the exact lane's answer does not depend on the visiting order */
-  RT_TRAVERSE_PER_RAY = 512u  /* never use the packet kernel: 32 independent rays per warp                  */
+  RT_TRAVERSE_PACKET  = 256u  /* near-first lanes, opt-in: one warp walks the tree ONCE for 32 consecutive rays of the
+                                 queue (one position, one stack, every node fetched once per warp) instead of 32
+                                 independent lanes.  Same hits (the exact lane's answer does not depend on the
+                                 visiting order).  Pays when consecutive rays visit the same nodes
+                                 (large triangles); on the 1M-triangle soup only 17 of 32 lanes want the node their
+                                 warp fetched and it is 20 % slower than independent lanes, which already get the
+                                 cache benefit of the pixel-major queue order (profiles/packet_kernel_r02.json)    */
 };
 int rt_scene_begin_frame(rt_scene* scene, void* stream);
 typedef struct rt_tile_set {    /* image partition for multi-GPU: tile t -> rank t % num_ranks      */
@@ -160,10 +160,55 @@ int rt_render(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_ti
 /* same, host buffers: device work + device->host copy of the image (main.cu:67-77) */
 int rt_render_host(rt_scene* scene, int w, int h, int aa, unsigned flags, const rt_tile_set* tiles,
                    uint8_t* h_rgba, int32_t* h_hit_id, uint8_t* h_written, rt_counters* counters);
+/* allocates the device image rt_render_host renders into (cudaMalloc of d_image, main.cu:56-58) ahead of the first frame */
+int rt_render_reserve(rt_scene* scene, int w, int h);
 /* closest hits for explicit rays (device arrays [n][3] origins and normalised directions):
  * hitNearest for a bounce!=0 ray (draw.cu:292-318).  Outputs device int32[n] / float[n]. */
 int rt_trace(rt_scene* scene, int n, const float* d_org, const float* d_dir, unsigned flags,
              int32_t* d_hit_id, float* d_hit_t, rt_counters* counters, void* stream);
+
+/* ---- multi-GPU -------------------------------------------------------------------
+ * No counterpart in the reference: it is a single-GPU program (main.cu:25-94, job.slurm:7-11).  The
+ * path shards by image tiles: the scene is replicated, every GPU builds the same LBVH itself and
+ * renders the tiles t with t % ranks == rank (rt_render's rt_tile_set), the owned tiles are gathered
+ * on the root.  rt_comm wraps one NCCL communicator (libnccl.so.2 is loaded when the first
+ * communicator is created, not before): either ONE process drives all GPUs (rt_comm_init, the C++
+ * host `raytracer --gpus N`), or there is one process per GPU (torchrun: rt_comm_unique_id on one
+ * rank, its 128 bytes handed to every rank by the host, rt_comm_init_rank everywhere).  Calls that
+ * take arrays (`scenes`, `d_rgba`, `streams`) index them by LOCAL device, 0..rt_comm_num_local-1. */
+typedef struct rt_comm rt_comm;
+int rt_comm_init(int ndev, const int* devices /* NULL = 0..ndev-1 */, rt_comm** out);
+int rt_comm_unique_id(void* id128);
+int rt_comm_init_rank(int nranks, int rank, const void* id128, int device, rt_comm** out);
+int rt_comm_destroy(rt_comm* comm);
+int rt_comm_size(const rt_comm* comm);                 /* GPUs in the communicator            */
+int rt_comm_num_local(const rt_comm* comm);            /* GPUs driven by this process         */
+int rt_comm_local_rank(const rt_comm* comm, int local);
+int rt_comm_local_device(const rt_comm* comm, int local);
+/* tile shape for `ranks` GPUs and an image `width` pixels wide: 256 pixels, tiles per row sharing as few
+ * factors with `ranks` as possible (else a rank owns whole columns of tiles) */
+void rt_tile_shape(int ranks, int width, int* tile_w, int* tile_h);
+/* copyConfigDataToDevice (src/config_utils.cu:72-199) on every GPU: the root's arrays (host or device
+ * pointers, as for rt_scene_create; root_desc is ignored in processes that do not own `root`) are
+ * broadcast over NCCL and each local GPU creates its arena from them.  scenes_out[num_local]. */
+int rt_scene_broadcast(rt_comm* comm, const rt_scene_desc* root_desc, int root, rt_scene** scenes_out);
+/* rt_scene_update_triangles on every GPU: 36 bytes per triangle from the root over NCCL.  Asynchronous
+ * on streams[local] (NULL: default streams). */
+int rt_comm_update_triangles(rt_comm* comm, rt_scene* const* scenes, const float* p0, const float* p1,
+                             const float* p2, int root, void* const* streams);
+int rt_comm_build_lbvh(rt_comm* comm, rt_scene* const* scenes, int morton_bits, unsigned flags, float* ms_out);
+/* d_rgba[local]: full-size device image holding the tiles that GPU rendered; afterwards the root's image
+ * holds all of them.  Every other GPU sends its own tiles only (1/ranks of the image), packed. */
+int rt_framebuffer_gather(rt_comm* comm, uint8_t* const* d_rgba, int w, int h, int tile_w, int tile_h,
+                          int root, void* const* streams);
+/* render() on every local GPU (one host thread each) + gather on `root` + optional copy of the root's
+ * image to h_rgba (main.cu:67-77).  tile_w/tile_h <= 0: rt_tile_shape. */
+/* device memory for hosts that do not link the CUDA runtime themselves (the per-GPU images of `raytracer --gpus N`) */
+void* rt_device_alloc(int device, size_t bytes);
+void  rt_device_free(int device, void* p);
+int rt_render_multi(rt_comm* comm, rt_scene* const* scenes, int w, int h, int aa, unsigned flags,
+                    int tile_w, int tile_h, int root, uint8_t* const* d_rgba, uint8_t* h_rgba,
+                    rt_counters* counters);
 
 /* ---- parity dumps in the reference's exact layouts ---------------------------------------------
  * codes: uint32[n] sorted d_morton_codes (config.hpp:109) (NULL ok); codes64: uint64[n] for

@@ -166,7 +166,7 @@ def synthetic_full_featured(n=4000, seed=11, rough=0.0):
     return cfg, a
 
 
-@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER, api.TRAVERSE_PACKET, api.TRAVERSE_PER_RAY])
+@pytest.mark.parametrize("flags", [0, api.TRAVERSE_NEAR_FIRST, api.TRAVERSE_REF_ORDER, api.TRAVERSE_PACKET])
 def test_render_all_shading_paths(flags):
     cfg, a = synthetic_full_featured()
     o = H.oracle_from_arrays(cfg, a)
@@ -536,8 +536,8 @@ def test_packet_kernel_gives_the_reference_order_hits():
 
 
 def test_packet_and_per_ray_renders_are_identical(monkeypatch):
-    """rt_render's default (packet kernel where the queue is coherent), RT_TRAVERSE_PACKET (every launch),
-    RT_TRAVERSE_PER_RAY (never) and the reference-order lane give the same bytes, ids and ray counts: 1 spp and
+    """rt_render's default (independent lanes), RT_TRAVERSE_PACKET (the packet kernel for every launch) and the
+    reference-order lane give the same bytes, ids and ray counts: 1 spp and
     multi-sample (pixel-major sample ids: 5, 16, 32 and 64 samples per pixel), sun + bulb shadow rays, mirrors + glass
     + GI, interleaved tiles, many small passes, queued and host-driven schedules."""
     cases = []
@@ -552,7 +552,7 @@ def test_packet_and_per_ray_renders_are_identical(monkeypatch):
         for aa, fl, (w, h), tiles in ((0, 0, (200, 120), None), (5, api.SPP_TRUE, (100, 60), None), (16, api.SPP_TRUE, (100, 60), api.TileSet(32, 8, 3, 1)),
                                       (32, 0, (60, 40), None), (64, api.SPP_TRUE, (40, 30), None), (20, 0, (60, 40), None)):
             ref = None
-            for pool, host_driven, lane in ((None, False, api.TRAVERSE_REF_ORDER), (None, False, 0), (None, False, api.TRAVERSE_PACKET), (None, False, api.TRAVERSE_PER_RAY),
+            for pool, host_driven, lane in ((None, False, api.TRAVERSE_REF_ORDER), (None, False, 0), (None, False, api.TRAVERSE_PACKET),
                                             (400_000, False, 0), (None, True, 0), (400_000, True, api.TRAVERSE_PACKET)):
                 if pool is None: monkeypatch.delenv("RT_POOL_BYTES", raising=False)
                 else: monkeypatch.setenv("RT_POOL_BYTES", str(pool))
@@ -567,3 +567,38 @@ def test_packet_and_per_ray_renders_are_identical(monkeypatch):
                 assert np.array_equal(r["rgba"], ref["rgba"]), "image differs (aa %d, lane %d, pool %s): %d bytes" % (aa, lane, pool, (r["rgba"] != ref["rgba"]).sum())
                 assert np.array_equal(r["ids"], ref["ids"]) and np.array_equal(r["written"], ref["written"])
                 assert r["counters"].rays == ref["counters"].rays and r["counters"].samples == ref["counters"].samples
+
+
+def test_exact_lane_on_tiny_far_spheres_with_grazing_rays():
+    """Small spheres far from the ray origins, rays aimed at their silhouettes: t = tc - sqrt(r^2 - d^2) cancels, the
+    accepted point can sit outside the sphere's AABB by more than 2e-3 r (the share of the slack that scales with r), and
+    the exact lane must still return the reference-order answer (traverse.cuh, RT_ORIGIN_SLACK; scene.cu, rt_sphere_slack).
+    Scene centred far from the coordinate origin as well, so that c - o rounds coarsely."""
+    rng = np.random.RandomState(77)
+    n = 30000
+    for shift, rmax in ((np.float32([0, 0, 0]), 2e-3), (np.float32([40, -30, 25]), 2e-3), (np.float32([300, 200, -100]), 1e-2)):
+        c = (rng.uniform(-1, 1, (n, 3)) + shift).astype(np.float32)
+        r = rng.uniform(rmax * 0.05, rmax, n).astype(np.float32)
+        cfg = synth.default_config(64, 64, 0, eye=tuple(shift + np.float32([0, 0, 3.5])))
+        mat = np.zeros((n, 11), np.float32); mat[:, :3] = 0.7; mat[:, 9] = 1.458
+        a = dict(sphere_c=c, sphere_r=r, sphere_mat=mat, refs=np.stack([np.zeros(n, np.int32), np.arange(n, dtype=np.int32)], 1),
+                 suns=np.array([[1, 1, 1, 1, 1, 1]], np.float32))
+        desc, keep = api.make_desc(cfg, a)
+        sc = api.Scene(desc, 0)
+        sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+        m = 400_000
+        k = rng.randint(0, n, m)
+        org = (shift + rng.uniform(-1, 1, (m, 3)) * rng.choice([2.0, 8.0, 40.0], (m, 1))).astype(np.float32)
+        to_c = c[k].astype(np.float64) - org
+        perp = np.cross(to_c, rng.normal(size=(m, 3))); perp /= np.linalg.norm(perp, axis=1, keepdims=True)
+        graze = (1.0 + rng.choice([-1e-2, -1e-3, -1e-4, -1e-5, 0.0, 1e-5, 1e-4, 1e-3], m))[:, None]
+        tgt = c[k].astype(np.float64) + perp * r[k][:, None] * graze
+        d = tgt - org; d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+        ri, rt_, _ = gpu_trace(sc, org, d, api.TRAVERSE_REF_ORDER)
+        ei, et, c1 = gpu_trace(sc, org, d, api.COUNTERS)
+        pi, pt, _ = gpu_trace(sc, org, d, api.TRAVERSE_PACKET)
+        assert (ri >= 0).mean() > 0.2
+        assert np.array_equal(ei, ri) and np.array_equal(et.view(np.uint32), rt_.view(np.uint32)), "shift %s: %d rays differ" % (shift, (ei != ri).sum())
+        assert np.array_equal(pi, ri) and np.array_equal(pt.view(np.uint32), rt_.view(np.uint32))
+        print("shift %s: hits %.3f, fallback rays %d of %d" % (shift, (ri >= 0).mean(), c1.fallback_rays, m))
+        sc.close()
