@@ -311,7 +311,11 @@ def run_b200(a):
     img_h = torch.zeros((Hh, W, 4), dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tiles = parallel.tile_set(world, rank, width=W)
-    rflags = api.SPP_TRUE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0) | (api.RENDER_OVERLAP_BUILD if a.overlap_build else 0)
+    # N > 1: a rank renders 1/N of the image but updates and builds the whole scene, so the frame's ray generation runs beside
+    # update + build (RT_RENDER_OVERLAP_BUILD) on the device leg too; at N = 1 generation fills the GPU anyway and the plain
+    # stream order keeps lbvh_build_ms the time of the build running alone
+    overlap_dev = a.overlap_build or world > 1
+    rflags = api.SPP_TRUE | (api.TRAVERSE_NEAR_FIRST if a.near_first else 0) | (api.RENDER_OVERLAP_BUILD if overlap_dev else 0)
     # launch durations of the dominant kernel (roofline) are taken with one pass at a time: with two passes in flight
     # (the default, and what `value` and `e2e` run) a launch's event interval includes waiting for the other pass's CTAs
     rflags_serial = rflags | api.TIME_TRAVERSE | api.RENDER_SERIAL_PASSES
@@ -448,7 +452,7 @@ def run_b200(a):
         "data": "synthetic",
         "config": {"workload": workload_name(a), "lane": ("near-first (not bit-exact)" if a.near_first else "exact near-first (bit-exact vs reference order)") + (", 4-wide tree (experimental)" if a.wide4 else ""),
                    "l2": "256 MiB flush write between timed steps; per-frame working set (state pool + scene) exceeds the 126 MB L2",
-                   "parallelism": "scene replicated, image in interleaved %dx%d tiles over %d GPU(s), NCCL broadcast + framebuffer reduce; two passes in flight per GPU" % (parallel.tile_shape(world, W) + (world,))},
+                   "parallelism": "scene replicated, image in interleaved %dx%d tiles over %d GPU(s), NCCL broadcast of the scene + gather of each rank's own tiles (rt_framebuffer_gather); two passes in flight per GPU%s" % (parallel.tile_shape(world, W) + (world, "; ray generation overlaps update + build" if overlap_dev else ""))},
         "ms_steps_rank0": {"device": [round(x, 3) for x in dev_res["steps_ms"]], "e2e": [round(x, 3) for x in e2e_res["steps_ms"]],
                            "serial_passes": [round(x, 3) for x in ser_res["steps_ms"]]},  # this rank's own event time of every timed step
         "ms_per_step_serial_passes": ser_res["ms"] / a.steps,

@@ -14,8 +14,15 @@
 namespace {
 
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 4096 keys
+// keys per thread: 16 (4096-key tiles) for large inputs; 8 (2048-key tiles) up to RT_SORT_SMALL_N keys, where a pass is a
+// few hundred tiles on 148 SMs and bound by the latency of one tile's chain (load, 16 dependent match rounds, look-back,
+// scatter; ncu: 20 % of the warp slots, 14 % issue): twice the tiles in flight, half the chain per tile
+#ifndef RT_SORT_TMA
+#define RT_SORT_TMA 0
+#endif
+#ifndef RT_SORT_SMALL_N
+#define RT_SORT_SMALL_N (4 << 20)
+#endif
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_VAL = (1u << 30) - 1;
 
@@ -36,7 +43,7 @@ __global__ void init_build_state_kernel(uint32_t* hist, int hist_words, uint32_t
 __global__ void __launch_bounds__(256) bounds_kernel(const float4* __restrict__ bv, int n, uint32_t* bounds_enc) {
   float mnx = INFINITY, mny = INFINITY, mnz = INFINITY, mxx = -INFINITY, mxy = -INFINITY, mxz = -INFINITY;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    float4 a = __ldg(bv + 3 * (size_t)i), b = __ldg(bv + 3 * (size_t)i + 1), c = __ldg(bv + 3 * (size_t)i + 2);
+    float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)i), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 2);
     RtBox bx = rt_prim_box(a, b, c);
     mnx = fminf(mnx, bx.xmin); mny = fminf(mny, bx.ymin); mnz = fminf(mnz, bx.zmin);
     mxx = fmaxf(mxx, bx.xmax); mxy = fmaxf(mxy, bx.ymax); mxz = fmaxf(mxz, bx.zmax);
@@ -98,7 +105,7 @@ __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ 
     const bool valid = i < n;
     KeyT code = 0;
     if (valid) {
-      float4 a = __ldg(bv + 3 * (size_t)i), b = __ldg(bv + 3 * (size_t)i + 1), c = __ldg(bv + 3 * (size_t)i + 2);
+      float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)i), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 2);
       float cx, cy, cz;
       if (c.w == RT_TAG_SPHERE) { cx = a.x; cy = a.y; cz = a.z; }  // lbvh_utils.cu:48-51
       else {  // (p0 + p1 + p2) / 3.0f, lbvh_utils.cu:55-58
@@ -132,7 +139,7 @@ __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ 
 __device__ inline uint32_t ld_volatile(const uint32_t* p) { return *(const volatile uint32_t*)p; }
 __device__ inline void st_volatile(uint32_t* p, uint32_t v) { *(volatile uint32_t*)p = v; }
 
-template <typename KeyT>
+template <typename KeyT, int SORT_ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __restrict__ kin, KeyT* __restrict__ kout,
                                                                const uint32_t* __restrict__ vin, uint32_t* __restrict__ vout, int n,
                                                                int shift, const uint32_t* __restrict__ hist, uint32_t* lookback,
@@ -142,6 +149,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
   __shared__ uint32_t s_lbase[256];             // local exclusive digit offsets
   __shared__ uint32_t s_scan[2][SORT_WARPS];
   __shared__ uint32_t s_tile;
+  constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
   extern __shared__ __align__(16) unsigned char s_raw[];
   KeyT* s_keys = reinterpret_cast<KeyT*>(s_raw);
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw);
@@ -167,6 +175,39 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
   KeyT key[SORT_ITEMS];
   uint32_t val[SORT_ITEMS], pos[SORT_ITEMS];
   const size_t wbase = base + (size_t)warp * (32 * SORT_ITEMS);
+#if RT_SORT_TMA
+  // EXPERIMENT (BASELINE.json: "TMA bulk staging on these streaming passes"), off by default: a full tile's keys and
+  // values come in with two cp.async.bulk copies (UBLKCP) that one thread issues and an mbarrier signals; the lanes
+  // then pick their items from shared memory.  Measured against the plain coalesced loads below: see DESIGN.md 4.1.
+  if (tile_valid == SORT_TILE) {
+    __shared__ __align__(8) unsigned long long s_bar;
+    KeyT* st_k = reinterpret_cast<KeyT*>(s_raw);
+    uint32_t* st_v = reinterpret_cast<uint32_t*>(s_raw + SORT_TILE * sizeof(KeyT));
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned bk = SORT_TILE * (unsigned)sizeof(KeyT), bvb = SORT_TILE * 4u;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bk + bvb) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"((unsigned)__cvta_generic_to_shared(st_k)),
+                   "l"(kin + base), "r"(bk), "r"(bar) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"((unsigned)__cvta_generic_to_shared(st_v)),
+                   "l"(vin + base), "r"(bvb), "r"(bar) : "memory");
+    }
+    unsigned done = 0;
+    while (!done)
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+#pragma unroll
+    for (int j = 0; j < SORT_ITEMS; j++) {
+      const int li = warp * (32 * SORT_ITEMS) + j * 32 + lane;
+      key[j] = st_k[li]; val[j] = st_v[li];
+    }
+    __syncthreads();  // the staging area is the scatter area below
+  } else
+#endif
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; j++) {
     size_t idx = wbase + (size_t)j * 32 + lane;
@@ -256,10 +297,11 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
   }
 }
 
-template <typename KeyT, int NPASS>
+template <typename KeyT, int NPASS, int ITEMS>
 int sort_impl(rt_scene* s, cudaStream_t st, uint32_t* launches) {
   const int n = s->n;
-  const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  constexpr int TILE = SORT_THREADS * ITEMS;
+  const int tiles = (n + TILE - 1) / TILE;
   KeyT *ka = (KeyT*)s->keys_a, *kb = (KeyT*)s->keys_b;
   uint32_t *pa = s->perm_a, *pb = s->perm_b;
   int grid = (n + 255) / 256;
@@ -267,8 +309,8 @@ int sort_impl(rt_scene* s, cudaStream_t st, uint32_t* launches) {
   morton_kernel<KeyT, NPASS><<<grid, 256, 0, st>>>(s->prim_bv, n, (const uint32_t*)s->bounds, ka, pa, s->hist, s->node_flags);
   (*launches)++;
   for (int p = 0; p < NPASS; p++) {
-    onesweep_kernel<KeyT><<<tiles, SORT_THREADS, SORT_TILE * sizeof(KeyT), st>>>(ka, kb, pa, pb, n, 8 * p, s->hist + 256 * p,
-                                                                              s->lookback + (size_t)p * tiles * 256, s->tickets + p);
+    onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, TILE * (sizeof(KeyT) + (RT_SORT_TMA ? 4 : 0)), st>>>(ka, kb, pa, pb, n, 8 * p, s->hist + 256 * p,
+                                                                                 s->lookback + (size_t)p * tiles * 256, s->tickets + p);
     (*launches)++;
     KeyT* tk = ka; ka = kb; kb = tk;
     uint32_t* tp = pa; pa = pb; pb = tp;
@@ -285,7 +327,9 @@ int sort_impl(rt_scene* s, cudaStream_t st, uint32_t* launches) {
 int rt_build_codes_and_sort(rt_scene* s, int morton_bits, unsigned flags, cudaStream_t st, uint32_t* launches) {
   const int n = s->n;
   const int npass = morton_bits == 30 ? 4 : 8;
-  const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  const bool small = n <= RT_SORT_SMALL_N;
+  const int tile_keys = SORT_THREADS * (small ? 8 : 16);
+  const int tiles = (n + tile_keys - 1) / tile_keys;
   float3 mn = make_float3(s->cfg.scene_min[0], s->cfg.scene_min[1], s->cfg.scene_min[2]);
   float3 mx = make_float3(s->cfg.scene_max[0], s->cfg.scene_max[1], s->cfg.scene_max[2]);
   if (flags & RT_BOUNDS_COMPUTED) { mn = make_float3(INFINITY, INFINITY, INFINITY); mx = make_float3(-INFINITY, -INFINITY, -INFINITY); }
@@ -299,6 +343,6 @@ int rt_build_codes_and_sort(rt_scene* s, int morton_bits, unsigned flags, cudaSt
     (*launches)++;
   }
   RT_CUDA(cudaGetLastError());
-  if (morton_bits == 30) return sort_impl<uint32_t, 4>(s, st, launches);
-  return sort_impl<uint64_t, 8>(s, st, launches);
+  if (morton_bits == 30) return small ? sort_impl<uint32_t, 4, 8>(s, st, launches) : sort_impl<uint32_t, 4, 16>(s, st, launches);
+  return small ? sort_impl<uint64_t, 8, 8>(s, st, launches) : sort_impl<uint64_t, 8, 16>(s, st, launches);
 }

@@ -79,9 +79,9 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const uint32_t p = perm[k];
-  const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
+  const float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)p), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 2);
   // gather the trace view into Morton order (leaf k <-> record k)
-  const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+  const float4 t0 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p), t1 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 1), t2 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 2);
   RtBox box = rt_prim_box(a, b, c);
   {
     float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
@@ -175,8 +175,8 @@ __global__ void __launch_bounds__(RT_BU_CHUNK) bottom_up_local_kernel(const KeyT
   RtBox box; uint32_t ref = 0; float slack = 0.f;
   if (k < n) {
     const uint32_t p = perm[k];
-    const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
-    const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+    const float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)p), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 2);
+    const float4 t0 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p), t1 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 1), t2 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 2);
     box = rt_prim_box(a, b, c);
     float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;  // the trace view in Morton order (leaf k <-> record k)
     rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
@@ -285,8 +285,8 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const uint32_t p = perm[k];
-  const float4 a = __ldg(bv + 3 * (size_t)p), b = __ldg(bv + 3 * (size_t)p + 1), c = __ldg(bv + 3 * (size_t)p + 2);
-  const float4 t0 = __ldg(tv + 3 * (size_t)p), t1 = __ldg(tv + 3 * (size_t)p + 1), t2 = __ldg(tv + 3 * (size_t)p + 2);
+  const float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)p), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 2);
+  const float4 t0 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p), t1 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 1), t2 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 2);
   RtBox box = rt_prim_box(a, b, c);
   {
     float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;

@@ -93,11 +93,10 @@ def write_scene_text(path, cfg, arrays, name="out.png"):
         t = arrays.get("tri")
         if t is not None:
             m = arrays["tri_mat"]
-            lines = []
-            for i in range(len(t[0])):
-                lines.append("color %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\ntri -3 -2 -1\n" % (
-                    m[i, 0], m[i, 1], m[i, 2], *t[0][i], *t[1][i], *t[2][i]))
-            f.write("".join(lines))
+            fmt = "color %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\nxyz %.9g %.9g %.9g\ntri -3 -2 -1\n"
+            rows = np.concatenate([m[:, :3], t[0], t[1], t[2]], axis=1).astype(np.float64)  # float32 -> double is exact, %.9g round-trips it
+            for lo in range(0, len(rows), 200_000):  # in pieces: a 10M-triangle scene is 1.8 GB of text
+                f.write("".join([fmt % tuple(r) for r in rows[lo:lo + 200_000].tolist()]))
         if arrays.get("sphere_c") is not None:
             m = arrays["sphere_mat"]; c = arrays["sphere_c"]; r = arrays["sphere_r"]
             f.write("".join("color %.9g %.9g %.9g\nsphere %.9g %.9g %.9g %.9g\n" % (m[i, 0], m[i, 1], m[i, 2], *c[i], r[i]) for i in range(len(c))))

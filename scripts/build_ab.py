@@ -1,0 +1,28 @@
+"""LBVH build time A/B: update_triangles -> rt_build_lbvh on the soup at 1M and 10M triangles, best and median of 12
+(CUDA events inside rt_build_lbvh).  usage: RT_LIB=.../libb200rt_x.so python scripts/build_ab.py [label]"""
+import os, statistics, sys
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from cuda_ray_tracer_b200 import api, synth
+label = sys.argv[1] if len(sys.argv) > 1 else os.path.basename(api.LIB_PATH)
+for n in (1_000_000, 10_000_000):
+    cfg, a = synth.soup(n, 1, 64, 64, 0)
+    p0, p1, p2 = a["tri"][:3]
+    nor, e1, e2 = api.triangle_setup(p0, p1, p2)
+    a["tri"] = [torch.from_numpy(x).cuda() for x in (p0, p1, p2, nor, e1, e2)]
+    desc, keep = api.make_desc(cfg, a)
+    sc = api.Scene(desc, 0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for bits in (30, 63):
+        ms = []
+        for k in range(12):
+            sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2]); flush.fill_(k); torch.cuda.synchronize()
+            ms.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED))
+        warm = []
+        for k in range(6):  # the frame loop's case: the vertex update has just written the records
+            sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2])
+            warm.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED))
+        print("%-10s n=%8d bits=%d  build after L2 flush: best %.3f median %.3f ms | right after update_triangles: best %.3f ms" % (
+            label, n, bits, min(ms), statistics.median(ms), min(warm)))
+    sc.close(); del sc, a
