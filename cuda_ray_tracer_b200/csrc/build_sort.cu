@@ -14,14 +14,15 @@
 namespace {
 
 constexpr int SORT_THREADS = 256;
-// keys per thread: 16 (4096-key tiles) for large inputs; 8 (2048-key tiles) up to RT_SORT_SMALL_N keys, where a pass is a
-// few hundred tiles on 148 SMs and bound by the latency of one tile's chain (load, 16 dependent match rounds, look-back,
-// scatter; ncu: 20 % of the warp slots, 14 % issue): twice the tiles in flight, half the chain per tile
-#ifndef RT_SORT_TMA
-#define RT_SORT_TMA 0
-#endif
+// keys per thread: 16 (4096-key tiles).  A pass over 1M keys is only 245 tiles on 148 SMs and bound by the latency of one
+// tile's chain (ncu: 20 % of the warp slots, 14 % issue), so 2048-key tiles (RT_SORT_SMALL_N = the key count up to which
+// they are used) were measured: 0.336 ms per build at 1M triangles against 0.328 with 4096-key tiles, 0.490 against 0.469
+// with 63-bit keys (profiles/build_ab_r02.txt) — the longer look-back chain costs what the shorter tile saves.  Off.
 #ifndef RT_SORT_SMALL_N
-#define RT_SORT_SMALL_N (4 << 20)
+#define RT_SORT_SMALL_N 0
+#endif
+#ifndef RT_SORT_TMA
+#define RT_SORT_TMA 0   // experiment: cp.async.bulk staging of the tile (see onesweep_kernel)
 #endif
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_VAL = (1u << 30) - 1;
@@ -178,8 +179,10 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
 #if RT_SORT_TMA
   // EXPERIMENT (BASELINE.json: "TMA bulk staging on these streaming passes"), off by default: a full tile's keys and
   // values come in with two cp.async.bulk copies (UBLKCP) that one thread issues and an mbarrier signals; the lanes
-  // then pick their items from shared memory.  Measured against the plain coalesced loads below: see DESIGN.md 4.1.
-  if (tile_valid == SORT_TILE) {
+  // then pick their items from shared memory (SASS: UBLKCP.S.G + SYNCS).  Measured against the plain coalesced loads
+  // below (profiles/build_ab_r02.txt): 0.336 vs 0.336 ms per build at 1M triangles, 2.528 vs 2.494 ms at 10M — the pass is
+  // bound by the ranking chain and the look-back, not by how the 32 KB tile arrives.
+  if (tile_valid == SORT_TILE && SORT_TILE * (sizeof(KeyT) + 4) <= 40 * 1024) {  // staging must fit beside the 9 KB of static shared memory
     __shared__ __align__(8) unsigned long long s_bar;
     KeyT* st_k = reinterpret_cast<KeyT*>(s_raw);
     uint32_t* st_v = reinterpret_cast<uint32_t*>(s_raw + SORT_TILE * sizeof(KeyT));
@@ -309,7 +312,7 @@ int sort_impl(rt_scene* s, cudaStream_t st, uint32_t* launches) {
   morton_kernel<KeyT, NPASS><<<grid, 256, 0, st>>>(s->prim_bv, n, (const uint32_t*)s->bounds, ka, pa, s->hist, s->node_flags);
   (*launches)++;
   for (int p = 0; p < NPASS; p++) {
-    onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, TILE * (sizeof(KeyT) + (RT_SORT_TMA ? 4 : 0)), st>>>(ka, kb, pa, pb, n, 8 * p, s->hist + 256 * p,
+    onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, TILE * (sizeof(KeyT) + ((RT_SORT_TMA && TILE * (sizeof(KeyT) + 4) <= 40 * 1024) ? 4 : 0)), st>>>(ka, kb, pa, pb, n, 8 * p, s->hist + 256 * p,
                                                                                  s->lookback + (size_t)p * tiles * 256, s->tickets + p);
     (*launches)++;
     KeyT* tk = ka; ka = kb; kb = tk;

@@ -315,8 +315,8 @@ __global__ void __launch_bounds__(256) refit_kernel(const uint32_t* __restrict__
 }
 
 // ---- 4-wide tree over the same leaves (RT_BUILD_WIDE4, experimental) ---------------------------------------
-// Wide node i (same slot as binary node i) holds up to four 32-byte halves: for each child of node i, the child's own
-// half if it is a leaf, else the two halves of the child node.  Unused places hold NaN boxes (never hit).  One thread
+// Wide node i (same slot as binary node i) holds up to four 32-byte halves in two pairs: for each child of node i, the
+// child's own half if it is a leaf (alone in its pair), else the two halves of the child node.  Unused places hold NaN boxes (never hit).  One thread
 // per slot; a slot that no wide step can reach (odd depth) is built as well, it costs nothing to have.
 __global__ void __launch_bounds__(256) collapse4_kernel(const float4* __restrict__ nodes, int n, float4* __restrict__ wnodes) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -325,20 +325,62 @@ __global__ void __launch_bounds__(256) collapse4_kernel(const float4* __restrict
   float4 out[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) out[k] = make_float4(nan, nan, nan, nan);
-  int c = 0;
+  // places 0,1: the left child's children (or the left child alone, a leaf); places 2,3: the right child's.  The
+  // traversal orders the pairs and the children inside a pair by entry distance (traverse.cuh).
   for (int side = 0; side < 2; side++) {
     const float4 h0 = nodes[4 * (size_t)i + 2 * side], h1 = nodes[4 * (size_t)i + 2 * side + 1];
     const uint32_t ref = __float_as_uint(h1.z);
-    if (ref & RT_LEAF_BIT) { out[2 * c] = h0; out[2 * c + 1] = h1; c++; }
+    const int c = 2 * side;
+    if (ref & RT_LEAF_BIT) { out[2 * c] = h0; out[2 * c + 1] = h1; out[2 * c + 3].z = __uint_as_float(0u); }  // ref word of the unused place
     else {
       const float4* g = nodes + 4 * (size_t)ref;
-      out[2 * c] = g[0]; out[2 * c + 1] = g[1]; c++;
-      out[2 * c] = g[2]; out[2 * c + 1] = g[3]; c++;
+      out[2 * c] = g[0]; out[2 * c + 1] = g[1];
+      out[2 * c + 2] = g[2]; out[2 * c + 3] = g[3];
     }
   }
-  for (int k = 2 * c; k < 8; k++) out[k].z = (k & 1) ? __uint_as_float(0u) : nan;  // ref word of an unused place
+#if RT_WIDE_BF16
+  // 96-byte node: every plane as a bfloat16 offset from the node's min corner, rounded OUTWARD and checked with the very
+  // addition the traversal decodes it with (traverse.cuh, rt_bf16pair_plus): fl(org + lo_off) <= lo and fl(org + hi_off) >= hi
+  // as fp32 numbers, so the decoded box contains the child's exact box.  Leaves keep their exact box in the leaf record;
+  // the traversal tests it before the primitive.
+  float org[3] = {INFINITY, INFINITY, INFINITY};
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const float4 h0 = out[2 * c], h1 = out[2 * c + 1];
+    if (h0.x == h0.x) { org[0] = fminf(org[0], h0.x); org[1] = fminf(org[1], h0.y); org[2] = fminf(org[2], h1.x); }
+  }
+  auto off_lo = [](float lo, float o) -> unsigned {  // largest bf16 offset with fl(o + off) <= lo
+    unsigned b = __float_as_uint(fmaxf(lo - o, 0.0f)) & 0xFFFF0000u;
+    while (b != 0u && !(o + __uint_as_float(b) <= lo)) b -= 0x10000u;
+    return b >> 16;
+  };
+  auto off_hi = [](float hi, float o) -> unsigned {  // smallest bf16 offset with fl(o + off) >= hi
+    unsigned b = (__float_as_uint(fmaxf(hi - o, 0.0f)) + 0xFFFFu) & 0xFFFF0000u;
+    while (b < 0x7F800000u && !(o + __uint_as_float(b) >= hi)) b += 0x10000u;
+    return b >> 16;
+  };
+  unsigned w[12]; float aux[4]; unsigned refs[4];
+#pragma unroll
+  for (int c = 0; c < 4; c++) {
+    const float4 h0 = out[2 * c], h1 = out[2 * c + 1];  // xmin ymin xmax ymax | zmin zmax ref aux
+    refs[c] = __float_as_uint(h1.z); aux[c] = h1.w;
+    if (h0.x == h0.x) {
+      w[3 * c + 0] = off_lo(h0.x, org[0]) | (off_lo(h0.y, org[1]) << 16);
+      w[3 * c + 1] = off_hi(h0.z, org[0]) | (off_hi(h0.w, org[1]) << 16);
+      w[3 * c + 2] = off_lo(h1.x, org[2]) | (off_hi(h1.y, org[2]) << 16);
+    } else { w[3 * c + 0] = w[3 * c + 1] = w[3 * c + 2] = 0x7FC07FC0u; refs[c] = 0u; aux[c] = 0.f; }  // unused place: NaN offsets never pass
+  }
+  float4* o6 = wnodes + 6 * (size_t)i;
+  o6[0] = make_float4(org[0], org[1], org[2], 0.f);
+  o6[1] = make_float4(__uint_as_float(refs[0]), __uint_as_float(refs[1]), __uint_as_float(refs[2]), __uint_as_float(refs[3]));
+  o6[2] = make_float4(__uint_as_float(w[0]), __uint_as_float(w[1]), __uint_as_float(w[2]), __uint_as_float(w[3]));
+  o6[3] = make_float4(__uint_as_float(w[4]), __uint_as_float(w[5]), __uint_as_float(w[6]), __uint_as_float(w[7]));
+  o6[4] = make_float4(__uint_as_float(w[8]), __uint_as_float(w[9]), __uint_as_float(w[10]), __uint_as_float(w[11]));
+  o6[5] = make_float4(aux[0], aux[1], aux[2], aux[3]);
+#else
 #pragma unroll
   for (int k = 0; k < 8; k++) wnodes[8 * (size_t)i + k] = out[k];
+#endif
 }
 
 // ---- export in the reference's layouts --------------------------------------------------------

@@ -1,10 +1,9 @@
 // common.cuh — internal types of libb200rt.so (device data layout, error handling).
 //
 // Data layout in HBM (all arrays 256-byte aligned inside one arena):
-//   prim_bv / prim_tv: interleaved, one 128-byte record per primitive (RT_PRIM_STRIDE), file order
-//   prim_bv  [n][3 of 8] float4  "build view".          triangle: p0.xyz p1.x | p1.yz p2.xy | p2.z slack 0 tag
+//   prim_bv  [n][3] float4  "build view", file order.   triangle: p0.xyz p1.x | p1.yz p2.xy | p2.z slack 0 tag
 //                                                      sphere:   c.xyz r      | 0 0 0 0     | 0 slack 0 tag
-//   prim_tv  [n][3 of 8] float4  "trace view".          triangle: p0.xyz nor.x | nor.yz e1.xy | e1.z e2.xyz
+//   prim_tv  [n][3] float4  "trace view", file order.   triangle: p0.xyz nor.x | nor.yz e1.xy | e1.z e2.xyz
 //                                                      sphere:   c.xyz r      | 0 ...
 //   prim_mat [n][3] float4  Materials (11 floats + pad), file order
 //   sorted_tv[n][6] float4  prim_tv gathered into Morton order (leaf k reads record k), 96-byte records:
@@ -25,11 +24,17 @@
 #include "../../include/rt_api.h"
 
 #define RT_TV_STRIDE 6  // float4 words per sorted leaf record (96 bytes = three 32-byte sectors)
-// File-order primitive record: ONE 128-byte line per primitive, build view in words 0..2, trace view in words 4..6
-// (prim_tv = prim_bv + 4; words 3 and 7 are written as zero so that a record is a full line).  The builder's gather
-// through the sorted permutation (bottom_up_kernel) is bound by the HBM random-access rate: one location per primitive
-// instead of two 48-byte records in two arrays.
-#define RT_PRIM_STRIDE 8
+// File-order primitive records: 48 bytes (three float4) per primitive in each of the two views.
+// (Measured and rejected, profiles/build_ab_r02.txt: ONE interleaved 128-byte record per primitive, so that the builder's
+// gather through the sorted permutation touches one location instead of two.  The gather got cheaper, but the two
+// streaming passes over the build view (bounds, Morton codes) then read 128-byte strides for 48 useful bytes: 0.336 ms
+// per build at 1M triangles against 0.302.)
+#define RT_PRIM_STRIDE 3
+// format of the 4-wide nodes (RT_BUILD_WIDE4): 0 = four fp32 child halves, 128 bytes; 1 = bfloat16 plane offsets from the
+// node's min corner, 96 bytes (build_tree.cu collapse4_kernel, traverse.cuh)
+#ifndef RT_WIDE_BF16
+#define RT_WIDE_BF16 0
+#endif
 #define RT_TAG_TRI 1.0f
 #define RT_TAG_SPHERE 2.0f
 

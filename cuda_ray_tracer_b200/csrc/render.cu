@@ -1017,7 +1017,17 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   if (const char* e = getenv("RT_PACKET")) pkt_mode = atoi(e);  // experiments
   const bool both = s->any_shiny && s->any_trans;
   const int gi = s->cfg.gi != 0 ? 1 : 0;
-  P.depth = 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
+  // Frames per sample.  Without mirrors, glass or GI the only frame a sample ever holds is the diffuse state of the hit
+  // whose shadow rays are in flight (pushed at level 0 by the visit that shades the primary hit): one level.  Otherwise
+  // the deepest stack is reached along a chain of reflections: every reflect call in progress keeps at most its own
+  // W_REFLECT frame plus the provisional refract(outer) frame below it (draw.cu:424) while the hit it found pushes its
+  // own gi / refract / reflect calls, i.e. two frames per nested bounce when a primitive is both shiny and transparent,
+  // bounded by `bounces` (each nested call runs with bounce - 1, draw.cu:404,474) or |gi| for the GI chain; one pending
+  // call otherwise.  + 2 for the frames of the innermost hit (pending call being expanded + diffuse state), + 1 with GI.
+  // tests/test_render_gpu.py::test_deep_recursion_fits_the_continuation_stack drives the worst case (every primitive shiny
+  // and transparent, bounces 16, ~90 000 rays per pixel) against the oracle's own recursion.
+  const bool full_shade = s->any_shiny || s->any_trans || s->cfg.gi != 0;
+  P.depth = !full_shade ? 1 : 2 + gi + (both ? 2 * std::max(std::max(s->cfg.bounces, std::abs(s->cfg.gi)), 1) + 2 : ((s->any_shiny || s->any_trans) ? 2 : 0));
   if (P.depth > 200) { rt_set_error("rt_render: bounces too large for the continuation stack"); return RT_ERR_INVALID; }
   P.rng_live = (s->any_rough || s->cfg.gi != 0) ? 1 : 0;
   P.full_shade = (s->any_shiny || s->any_trans || s->cfg.gi != 0) ? 1 : 0;
@@ -1217,7 +1227,9 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   const int nl = P.num_lights;
   const bool queued = !P.full_shade && nl + 2 <= 16 && getenv("RT_HOST_DRIVEN") == nullptr;
   const long long npasses_total = npix_pass > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
-  if (queued && npasses_total > 0) {
+  // (a lambda: RT_CUDA returns from IT, so a failure inside lands in the common error path below, which waits for the
+  // kernels already queued on the pass and head streams before the call returns — as the host-driven loop does)
+  auto run_queued = [&]() -> int {
     const size_t words = (size_t)npasses_total * 256;
     if (words > rs->h_blocks_words) {
       if (rs->h_blocks) cudaFreeHost(rs->h_blocks);
@@ -1271,14 +1283,23 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       RT_CUDA(cudaGetLastError());
       RT_CUDA(cudaMemcpyAsync(rs->h_blocks + 256 * pi, c.counters, (size_t)(nl + 2) * 64, cudaMemcpyDeviceToHost, c.st));
     }
-  } else {
+    return RT_OK;
+  };
+  if (queued && npasses_total > 0) err = run_queued();
+  else {
     for (int k = 0; k < nctx && err == RT_OK && next_slot0 < nslots; k++) err = start_pass(ctx[k]);
     while (err == RT_OK && (ctx[0].active || ctx[1].active))
       for (int k = 0; k < nctx && err == RT_OK; k++)
         if (ctx[k].active) err = advance(ctx[k]);
   }
 #undef RT_PASS_CUDA
-  if (err != RT_OK) { const std::string keep = rt_last_error(); cudaDeviceSynchronize(); rt_set_error(keep); return err; }  // nothing of this frame stays in flight
+  if (err != RT_OK) {  // nothing of this frame stays in flight, and the caller's stream gets its default L2 policy back
+    const std::string keep = rt_last_error();
+    cudaDeviceSynchronize();
+    if (l2win) for (int k = 0; k < nctx; k++) set_node_window(s, ctx[k].st, false);
+    rt_set_error(keep);
+    return err;
+  }
   if (!head_joined) {  // nothing to render: the clears still belong to this call
     RT_CUDA(cudaEventRecord(rs->ev_join, hs));
     RT_CUDA(cudaStreamWaitEvent(st, rs->ev_join, 0));

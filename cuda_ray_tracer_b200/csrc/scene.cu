@@ -36,7 +36,6 @@ __global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* ma
     tv[RT_PRIM_STRIDE * (size_t)i + 0] = make_float4(c[0], c[1], c[2], rad);
     tv[RT_PRIM_STRIDE * (size_t)i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     tv[RT_PRIM_STRIDE * (size_t)i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
-    bv[RT_PRIM_STRIDE * (size_t)i + 3] = make_float4(0.f, 0.f, 0.f, 0.f); tv[RT_PRIM_STRIDE * (size_t)i + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
     m = a.sm + 11 * (size_t)r.y;
   } else {
     size_t t = (size_t)r.y;
@@ -51,7 +50,6 @@ __global__ void pack_prims_kernel(PackArgs a, float4* bv, float4* tv, float4* ma
     bc.y = rt_leaf_slack(ba, bb, bc, ta, tb, tc, rt_prim_box(ba, bb, bc));  // hit slack, a property of the triangle setup
     bv[RT_PRIM_STRIDE * (size_t)i + 2] = bc;
     tv[RT_PRIM_STRIDE * (size_t)i + 0] = ta; tv[RT_PRIM_STRIDE * (size_t)i + 1] = tb; tv[RT_PRIM_STRIDE * (size_t)i + 2] = tc;
-    bv[RT_PRIM_STRIDE * (size_t)i + 3] = make_float4(0.f, 0.f, 0.f, 0.f); tv[RT_PRIM_STRIDE * (size_t)i + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
     tri_prim[t] = (uint32_t)i;
     m = a.tm + 11 * t;
   }
@@ -117,7 +115,6 @@ __global__ void update_tris_kernel(int nt, const float* p0a, const float* p1a, c
   bc.y = rt_leaf_slack(ba, bb, bc, ta, tb, tc, rt_prim_box(ba, bb, bc));  // hit slack travels with the triangle setup
   bv[RT_PRIM_STRIDE * i + 0] = ba; bv[RT_PRIM_STRIDE * i + 1] = bb; bv[RT_PRIM_STRIDE * i + 2] = bc;
   tv[RT_PRIM_STRIDE * i + 0] = ta; tv[RT_PRIM_STRIDE * i + 1] = tb; tv[RT_PRIM_STRIDE * i + 2] = tc;
-  bv[RT_PRIM_STRIDE * i + 3] = make_float4(0.f, 0.f, 0.f, 0.f); tv[RT_PRIM_STRIDE * i + 3] = make_float4(0.f, 0.f, 0.f, 0.f);  // full 128-byte line
 }
 
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -179,7 +176,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   const size_t tiles_max = n1 / 2048 + 2;  // onesweep tiles are >= 2048 keys
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align_up(bytes ? bytes : 16); return o; };
-  size_t o_bv = carve(n1 * 16 * RT_PRIM_STRIDE), o_mat = carve(n1 * 48), o_stv = carve(n1 * 16 * RT_TV_STRIDE), o_nodes = carve(n1 * 64);
+  size_t o_bv = carve(n1 * 16 * RT_PRIM_STRIDE), o_tv = carve(n1 * 16 * RT_PRIM_STRIDE), o_mat = carve(n1 * 48), o_stv = carve(n1 * 16 * RT_TV_STRIDE), o_nodes = carve(n1 * 64);
   size_t o_wn = carve(n1 * 128);
   size_t o_refs = carve(n1 * 8), o_tp = carve((size_t)(s->nt > 0 ? s->nt : 1) * 4);
   size_t o_sun = carve((size_t)d->num_suns * sizeof(LightSun)), o_bulb = carve((size_t)d->num_bulbs * sizeof(LightBulb)),
@@ -191,7 +188,7 @@ extern "C" int rt_scene_create(const rt_scene_desc* d, int device, rt_scene** ou
   cudaError_t e = cudaMalloc((void**)&s->arena, s->arena_bytes);
   if (e != cudaSuccess) { rt_set_error(std::string("rt_scene_create: arena cudaMalloc: ") + cudaGetErrorString(e)); delete s; return RT_ERR_NOMEM; }
   char* A = s->arena;
-  s->prim_bv = (float4*)(A + o_bv); s->prim_tv = s->prim_bv + 4; s->prim_mat = (float4*)(A + o_mat);
+  s->prim_bv = (float4*)(A + o_bv); s->prim_tv = (float4*)(A + o_tv); s->prim_mat = (float4*)(A + o_mat);
   s->sorted_tv = (float4*)(A + o_stv); s->nodes = (float4*)(A + o_nodes); s->wnodes = (float4*)(A + o_wn); s->refs = (int2*)(A + o_refs);
   s->tri_prim = (uint32_t*)(A + o_tp); s->suns = (LightSun*)(A + o_sun); s->bulbs = (LightBulb*)(A + o_bulb);
   s->planes = (PlaneRec*)(A + o_pl); s->keys_a = (uint64_t*)(A + o_ka); s->keys_b = (uint64_t*)(A + o_kb);

@@ -94,12 +94,32 @@ __device__ __forceinline__ RtRay2 rt_ray2(const V3 o, const V3 inv) {
 __device__ __forceinline__ V3 rt_ray2_o(const RtRay2& q) { float x, y, z, z2; rt_unpack2(q.oxy, x, y); rt_unpack2(q.ozz, z, z2); return mk3(x, y, z); }
 __device__ __forceinline__ V3 rt_ray2_inv(const RtRay2& q) { float x, y, z, z2; rt_unpack2(q.ixy, x, y); rt_unpack2(q.izz, z, z2); return mk3(x, y, z); }
 template <bool INCLUSIVE>
-__device__ __forceinline__ bool rt_slab_tn2(const float4 h0, const float4 h1, const RtRay2& q, const float tmax, float& enter, V3& tn) {
+__device__ __forceinline__ bool rt_slab_pairs(const unsigned long long lo_xy, const unsigned long long hi_xy, const unsigned long long zz, const RtRay2& q,
+                                              const float tmax, float& enter, V3& tn) {
   float tx1, ty1, tx2, ty2, tz1, tz2;
-  rt_unpack2(rt_submul2(rt_pack2(h0.x, h0.y), q.oxy, q.ixy), tx1, ty1);
-  rt_unpack2(rt_submul2(rt_pack2(h0.z, h0.w), q.oxy, q.ixy), tx2, ty2);
-  rt_unpack2(rt_submul2(rt_pack2(h1.x, h1.y), q.ozz, q.izz), tz1, tz2);
+  rt_unpack2(rt_submul2(lo_xy, q.oxy, q.ixy), tx1, ty1);
+  rt_unpack2(rt_submul2(hi_xy, q.oxy, q.ixy), tx2, ty2);
+  rt_unpack2(rt_submul2(zz, q.ozz, q.izz), tz1, tz2);
   return rt_slab_finish<INCLUSIVE>(tx1, tx2, ty1, ty2, tz1, tz2, tmax, enter, tn);
+}
+template <bool INCLUSIVE>
+__device__ __forceinline__ bool rt_slab_tn2(const float4 h0, const float4 h1, const RtRay2& q, const float tmax, float& enter, V3& tn) {
+  return rt_slab_pairs<INCLUSIVE>(rt_pack2(h0.x, h0.y), rt_pack2(h0.z, h0.w), rt_pack2(h1.x, h1.y), q, tmax, enter, tn);
+}
+// RT_WIDE_BF16: the 4-wide node stores every child plane as a bfloat16 OFFSET from the node's min corner (96-byte nodes,
+// three 32-byte fetches for four boxes instead of four).  A pair of offsets packed in one word becomes an f32x2 pair with
+// a shift and a mask, and one packed add of the corner gives fp32 plane coordinates: lo = fl(org + off).  The builder
+// (collapse4_kernel) rounds the offsets outward and CHECKS them with this very addition, so the decoded box contains the
+// child's exact box as fp32 numbers and everything downstream is the exact test's own arithmetic on a slightly larger
+// box — the monotonicity the exact lane relies on holds as it is.
+#ifndef RT_WIDE_BF16
+#define RT_WIDE_BF16 0
+#endif
+__device__ __forceinline__ unsigned long long rt_bf16pair_plus(const unsigned w, const unsigned long long org2) {
+  unsigned long long p, r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(p) : "r"(w << 16), "r"(w & 0xFFFF0000u));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(p), "l"(org2));
+  return r;
 }
 
 // 256-bit read-only load (LDG.E.256 on sm_100a): one instruction per 32-byte node half / leaf record half
@@ -343,10 +363,6 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 #define RT_WIDE_MIN_CTAS 9   // 4-wide instantiations (experimental): resident CTAs per SM the compiler must allow (56 registers; measured
                              // 3445 Mrays/s against 3397 at 8 CTAs / 64 registers and 3325 at 7 / 70)
 #endif
-#ifndef RT_WIDE_SORT
-#define RT_WIDE_SORT 1       // closest-hit rays: 1 = all hit children sorted by entry distance, 0 = nearest next, the rest in child order
-                             // (measured: 14.6 instead of 14.0 steps per ray and 4 % slower)
-#endif
 enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };  // per-ray flags of the near-first kernels
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
 // box on its path is entered before the reference's running tmax at that moment.  Entry distances grow down a
@@ -362,15 +378,23 @@ do {                                                                            
     if (COUNT) n_leaves++;                                                                                        \
     float th_;                                                                                                    \
     const V3 o = rt_ray2_o(q2);                                                                                   \
-    if (rt_prim_test(sc.sorted_tv, ref_, o, d, th_) && th_ > 1e-6f) { /* bvh_traversal.cu:80-86 */               \
+    float e_own_ = 0.f; bool own_ok_ = true;                                                                      \
+    if (LEAF_BOX_FIRST) { /* compressed wide nodes: the leaf's OWN exact box decides whether it is a candidate */   \
+      float4 b0_, b1_; rt_ld256(sc.sorted_tv + RT_TV_STRIDE * (size_t)((ref_) & RT_LEAF_MASK) + 4, b0_, b1_);      \
+      V3 tn_; own_ok_ = rt_slab_tn2<true>(b0_, b1_, q2, INFINITY, e_own_, tn_);                                   \
+    }                                                                                                             \
+    if (own_ok_ && rt_prim_test(sc.sorted_tv, ref_, o, d, th_) && th_ > 1e-6f) { /* bvh_traversal.cu:80-86 */    \
       const bool anyhit_ = SUN || (fl & F_ANYHIT);                                                                \
       bool take_ = th_ < tmax;                                                                                    \
       if (!anyhit_ && th_ == tmax && best >= 0 && ((ref_) & RT_LEAF_MASK) < ((unsigned)best & RT_LEAF_MASK)) take_ = true; \
       if (take_) {                                                                                                \
         if (EXACT && !SUN && (fl & F_WANTKEY)) {                                                                  \
           /* entry distance of the leaf's own box, with the exact test's arithmetic (third sector of the record) */ \
-          float4 b0_, b1_; rt_ld256(sc.sorted_tv + RT_TV_STRIDE * (size_t)((ref_) & RT_LEAF_MASK) + 4, b0_, b1_);  \
-          float e_; V3 tn_; rt_slab_tn2<true>(b0_, b1_, q2, INFINITY, e_, tn_);                                   \
+          float e_ = e_own_;                                                                                      \
+          if (!LEAF_BOX_FIRST) {                                                                                  \
+            float4 b0_, b1_; rt_ld256(sc.sorted_tv + RT_TV_STRIDE * (size_t)((ref_) & RT_LEAF_MASK) + 4, b0_, b1_); \
+            V3 tn_; rt_slab_tn2<true>(b0_, b1_, q2, INFINITY, e_, tn_);                                           \
+          }                                                                                                       \
           const bool cons_ = e_ < th_;                                                                            \
           if (anyhit_) { if (!cons_) fl |= F_FALLBACK; } /* bulb shadow ray: first consistent occluder */         \
           else {                                                                                                  \
@@ -391,6 +415,7 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
                                                                        unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
   // the two values are needed once per chunk of rays: kept in shared memory, not in two registers of every thread
   // (56 registers = 9 CTAs per SM; 59 = 8)
+  constexpr bool LEAF_BOX_FIRST = WIDE && RT_WIDE_BF16;
   __shared__ unsigned s_range[2];
   if (threadIdx.x == 0) { const unsigned nn = n_dev ? *n_dev : n_in; s_range[0] = nn; s_range[1] = (n_dev && cap_back) ? cap_back - nn : first_in; }
   __syncthreads();
@@ -545,51 +570,86 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
     }
 #else
     if (WIDE && !leaf_phase && act && !atleaf) {
-      // ---- node phase, 4-wide tree (RT_BUILD_WIDE4, experimental): one step = the four grandchildren ----
+      // ---- node phase, 4-wide tree (RT_BUILD_WIDE4): one step = the four grandchildren of a binary node ----
       // Half the dependent steps per ray for the same box tests (profiles/wide_tree_steps_r01.json).  Every child is
       // tested exactly like a child of the binary step (order-independent box test, slack-inflated culling key), so
       // the set of leaves reached differs from the binary lane's only by subtrees the intermediate node would have
       // culled — and the exact lane's answer does not depend on the order or the tree (its definition is on leaves).
+      // Places 0,1 hold the children of the binary node's left child, places 2,3 those of its right child (a leaf child
+      // sits alone in its pair; the empty place holds a NaN box, which fails the test).
+      // ORDER: what two binary steps would do — the pair whose nearer hit child is nearer first, inside a pair the
+      // nearer child first — from three comparisons, no sorting network: child i gets a 2-bit visiting rank, the hit
+      // children are written to their stack slots directly (slot = sp + number of hit children visited after it), the
+      // first visited one becomes the next position.  No (distance, key, reference) triples move between registers.
       if (COUNT) n_nodes++;
+      float e[4], k[4]; unsigned rf[4]; bool h[4];
+#if RT_WIDE_BF16
+      // 96-byte node: (org.xyz, -) (ref0..3) | 12 words of bf16 offset pairs, child c = words 3c..3c+2 = (xlo,ylo) (xhi,yhi) (zlo,zhi) | aux0..3
+      const float4* np = sc.wnodes + 6 * (size_t)cur;
+      float4 n0, n1, w0, w1, w2, ax;
+      rt_ld256(np, n0, n1); rt_ld256(np + 2, w0, w1); rt_ld256(np + 4, w2, ax);
+      const unsigned long long oxy = rt_pack2(n0.x, n0.y), ozz = rt_pack2(n0.z, n0.z);
+      const unsigned wd[12] = {__float_as_uint(w0.x), __float_as_uint(w0.y), __float_as_uint(w0.z), __float_as_uint(w0.w), __float_as_uint(w1.x), __float_as_uint(w1.y),
+                               __float_as_uint(w1.z), __float_as_uint(w1.w), __float_as_uint(w2.x), __float_as_uint(w2.y), __float_as_uint(w2.z), __float_as_uint(w2.w)};
+      const float axv[4] = {ax.x, ax.y, ax.z, ax.w};
+      rf[0] = __float_as_uint(n1.x); rf[1] = __float_as_uint(n1.y); rf[2] = __float_as_uint(n1.z); rf[3] = __float_as_uint(n1.w);
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        V3 tn;
+        h[c] = rt_slab_pairs<true>(rt_bf16pair_plus(wd[3 * c], oxy), rt_bf16pair_plus(wd[3 * c + 1], oxy), rt_bf16pair_plus(wd[3 * c + 2], ozz), q2,
+                                   (EXACT || SUN) ? INFINITY : tmax, e[c], tn);  // NaN offsets (unused place) fail
+        k[c] = e[c];
+        if (EXACT && !SUN) { k[c] = rt_key_inflated(tn, axv[c], rt_ray2_inv(q2), omk); h[c] = h[c] && !(k[c] > tcut); }
+        if (!h[c]) e[c] = INFINITY;
+      }
+#else
       const float4* np = sc.wnodes + 8 * (size_t)cur;
-      float e[4], k[4]; unsigned rf[4];
 #pragma unroll
       for (int c = 0; c < 4; c++) {
         float4 a, b;
         rt_ld256(np + 2 * c, a, b);
         V3 tn;
-        bool h = rt_slab_tn2<true>(a, b, q2, (EXACT || SUN) ? INFINITY : tmax, e[c], tn);  // a NaN box (unused place) fails
+        h[c] = rt_slab_tn2<true>(a, b, q2, (EXACT || SUN) ? INFINITY : tmax, e[c], tn);  // a NaN box (unused place) fails
         rf[c] = __float_as_uint(b.z);
         k[c] = e[c];
-        if (EXACT && !SUN) { k[c] = rt_key_inflated(tn, b.w, rt_ray2_inv(q2), omk); h = h && !(k[c] > tcut); }
-        if (!h) e[c] = INFINITY;  // sorts last; a box that passes is never entered at +INF
+        if (EXACT && !SUN) { k[c] = rt_key_inflated(tn, b.w, rt_ray2_inv(q2), omk); h[c] = h[c] && !(k[c] > tcut); }
+        if (!h[c]) e[c] = INFINITY;  // a box that passes is never entered at +INF
       }
-      if (!SUN && RT_WIDE_SORT) {
-        // ascending by entry distance: (0,1) (2,3) (0,2) (1,3) (1,2)
-#define RT_CSWAP(i_, j_) do { if (e[j_] < e[i_]) { const float te_ = e[i_]; e[i_] = e[j_]; e[j_] = te_; const float tk_ = k[i_]; k[i_] = k[j_]; k[j_] = tk_; \
-                                                   const unsigned tr_ = rf[i_]; rf[i_] = rf[j_]; rf[j_] = tr_; } } while (0)
-        RT_CSWAP(0, 1); RT_CSWAP(2, 3); RT_CSWAP(0, 2); RT_CSWAP(1, 3); RT_CSWAP(1, 2);
-#undef RT_CSWAP
-        // the nearest hit child next, the others on the stack with the nearest of them on top
-        if (e[3] < INFINITY) RT_PUSH(rf[3], k[3]);
-        if (e[2] < INFINITY) RT_PUSH(rf[2], k[2]);
-        if (e[1] < INFINITY) RT_PUSH(rf[1], k[1]);
-        cur = rf[0];
-        need_pop = !(e[0] < INFINITY);
-      } else {
-        // the nearest hit child next; the other hit children go on the stack in child order (their culling keys still
-        // prune them at pop time).  Sun shadow rays want any candidate: no order at all, the first hit child is taken.
-        float eb = e[0]; unsigned rb = rf[0]; int ib = 0;
-#pragma unroll
-        for (int c = 1; c < 4; c++) {
-          const bool lt = SUN ? (!(eb < INFINITY) && e[c] < INFINITY) : (e[c] < eb);
-          eb = lt ? e[c] : eb; rb = lt ? rf[c] : rb; ib = lt ? c : ib;
+#endif
+      const unsigned fl_ = e[1] < e[0] ? 1u : 0u, fr_ = e[3] < e[2] ? 1u : 0u;
+      const unsigned ft_ = fminf(e[2], e[3]) < fminf(e[0], e[1]) ? 1u : 0u;
+      const unsigned rk0 = (ft_ << 1) | fl_, rk1 = (ft_ << 1) | (fl_ ^ 1u), rk2 = ((ft_ ^ 1u) << 1) | fr_, rk3 = ((ft_ ^ 1u) << 1) | (fr_ ^ 1u);
+      const unsigned hr = ((unsigned)h[0] << rk0) | ((unsigned)h[1] << rk1) | ((unsigned)h[2] << rk2) | ((unsigned)h[3] << rk3);  // hits in visiting order
+      const int nhit = __popc(hr);
+      need_pop = nhit == 0;
+      if (nhit > 0) {
+        const int b0_ = __popc(hr >> (rk0 + 1)), b1_ = __popc(hr >> (rk1 + 1)), b2_ = __popc(hr >> (rk2 + 1)), b3_ = __popc(hr >> (rk3 + 1));  // hit children visited after child i
+        const int first = nhit - 1;
+        if (h[0] && b0_ == first) cur = rf[0];
+        if (h[1] && b1_ == first) cur = rf[1];
+        if (h[2] && b2_ == first) cur = rf[2];
+        if (h[3] && b3_ == first) cur = rf[3];
+        if (sp + first <= RT_STACK_SHARED) {  // all in shared memory: one predicated store per child
+          if (SUN) {
+            if (h[0] && b0_ != first) s_ref[sp + b0_][tid] = rf[0];
+            if (h[1] && b1_ != first) s_ref[sp + b1_][tid] = rf[1];
+            if (h[2] && b2_ != first) s_ref[sp + b2_][tid] = rf[2];
+            if (h[3] && b3_ != first) s_ref[sp + b3_][tid] = rf[3];
+          } else {
+            if (h[0] && b0_ != first) s_ent[sp + b0_][tid] = make_uint2(rf[0], __float_as_uint(k[0]));
+            if (h[1] && b1_ != first) s_ent[sp + b1_][tid] = make_uint2(rf[1], __float_as_uint(k[1]));
+            if (h[2] && b2_ != first) s_ent[sp + b2_][tid] = make_uint2(rf[2], __float_as_uint(k[2]));
+            if (h[3] && b3_ != first) s_ent[sp + b3_][tid] = make_uint2(rf[3], __float_as_uint(k[3]));
+          }
+          sp += first;
+        } else {  // deep stack (rare): one entry at a time through the shared / local / overflow cases, last visited first
+          for (int want = 0; want < first; want++) {
+            if (h[0] && b0_ == want) RT_PUSH(rf[0], k[0]);
+            if (h[1] && b1_ == want) RT_PUSH(rf[1], k[1]);
+            if (h[2] && b2_ == want) RT_PUSH(rf[2], k[2]);
+            if (h[3] && b3_ == want) RT_PUSH(rf[3], k[3]);
+          }
         }
-#pragma unroll
-        for (int c = 3; c >= 0; c--)
-          if (c != ib && e[c] < INFINITY) RT_PUSH(rf[c], k[c]);
-        cur = rb;
-        need_pop = !(eb < INFINITY);
       }
     }
     if (!WIDE && !leaf_phase && act && !atleaf) {
@@ -684,6 +744,7 @@ __global__ void __launch_bounds__(RT_PKT_THREADS, RT_PKT_MIN_CTAS) traverse_pack
   __shared__ unsigned s_range[2];
   if (threadIdx.x == 0) { const unsigned nn = n_dev ? *n_dev : n_in; s_range[0] = nn; s_range[1] = (n_dev && cap_back) ? cap_back - nn : first_in; }
   __syncthreads();
+  constexpr bool LEAF_BOX_FIRST = false;  // binary nodes hold the leaves' exact boxes
   // warp-uniform stack entry: (reference, smallest culling key among the lanes that want it, their lane mask)
   __shared__ uint4 s_stk[RT_PKT_THREADS / 32][RT_STACK_TOTAL];
   uint4* const stk = s_stk[threadIdx.x >> 5];

@@ -9,7 +9,7 @@ from cuda_ray_tracer_b200 import api, synth
 W, H, N = 3840, 2160, 1_000_000
 cfg, arrays = synth.soup(N, 1, W, H, 0); arrays = synth.finish_triangles(arrays)
 desc, keep = api.make_desc(cfg, arrays)
-sc = api.Scene(desc, 0); sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+sc = api.Scene(desc, 0); sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED | (api.BUILD_WIDE4 if os.environ.get('RT_WIDE4') else 0))  # RT_WIDE4=1: the 4-wide tree
 dev = torch.device("cuda", 0)
 # primary rays of the frame in row-major pixel order (struct.cu:16-62, no jitter), 3 samples per pixel -> 24.9M rays
 ys, xs = torch.meshgrid(torch.arange(H, device=dev, dtype=torch.float32), torch.arange(W, device=dev, dtype=torch.float32), indexing="ij")

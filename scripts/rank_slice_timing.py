@@ -8,7 +8,7 @@ from cuda_ray_tracer_b200 import api, synth, parallel
 W, H, SPP, N = 3840, 2160, 16, 1_000_000
 cfg, arrays = synth.soup(N, 1, W, H, SPP); arrays = synth.finish_triangles(arrays)
 desc, keep = api.make_desc(cfg, arrays)
-sc = api.Scene(desc, 0); sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
+sc = api.Scene(desc, 0); sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED | (api.BUILD_WIDE4 if os.environ.get('RT_WIDE4') else 0))  # RT_WIDE4=1: the 4-wide tree
 img = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda:0")
 def run(tiles, label):
     best = None

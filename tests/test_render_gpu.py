@@ -602,3 +602,50 @@ def test_exact_lane_on_tiny_far_spheres_with_grazing_rays():
         assert np.array_equal(pi, ri) and np.array_equal(pt.view(np.uint32), rt_.view(np.uint32))
         print("shift %s: hits %.3f, fallback rays %d of %d" % (shift, (ri >= 0).mean(), c1.fallback_rays, m))
         sc.close()
+
+
+def hall_of_mirrors(bounces, gi=0, n=160, seed=31):
+    """the worst case for the continuation stack: EVERY primitive is shiny and transparent (each hit leaves a reflect
+    and a refract call pending, and every reflection hit adds the provisional refract of the outer pair, draw.cu:424), the
+    camera sits inside a shell of big spheres and triangles so that almost no ray escapes, plus a shiny plane"""
+    rng = np.random.RandomState(seed)
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    c = (d * rng.uniform(1.2, 2.0, (n, 1))).astype(np.float32)
+    r = rng.uniform(0.4, 0.7, n).astype(np.float32)
+    sm = np.zeros((n, 11), np.float32); sm[:, :3] = rng.uniform(0.3, 1, (n, 3)); sm[:, 3:6] = 0.5; sm[:, 6:9] = 0.6; sm[:, 9] = 1.3
+    nt = 40
+    tc = (rng.normal(size=(nt, 3)) * 0.8).astype(np.float32)
+    p0 = tc; p1 = (tc + rng.uniform(-0.5, 0.5, (nt, 3))).astype(np.float32); p2 = (tc + rng.uniform(-0.5, 0.5, (nt, 3))).astype(np.float32)
+    tm = np.zeros((nt, 11), np.float32); tm[:, :3] = 0.8; tm[:, 3:6] = 0.4; tm[:, 6:9] = 0.5; tm[:, 9] = 1.5
+    kinds = np.array([0] * n + [1] * nt, np.int32); ids = np.r_[np.arange(n), np.arange(nt)].astype(np.int32)
+    cfg = synth.default_config(16, 12, 0, eye=(0, 0, 0), bounces=bounces, gi=gi, expose=2.0)
+    a = dict(sphere_c=c, sphere_r=r, sphere_mat=sm, tri=[p0, p1, p2, None, None, None], tri_mat=tm, refs=np.stack([kinds, ids], 1),
+             suns=np.array([[1, 2, 1.5, 1, 1, 0.9]], np.float32), bulbs=np.array([[0.1, 0.2, 0.1, 2, 2, 2]], np.float32),
+             planes=np.array([[0, 1, 0, 2.5] + [0, 1, 0] + [0, -2.5, 0] + [0.6, 0.6, 0.7, 0.3, 0.3, 0.3, 0.2, 0.2, 0.2, 1.458, 0]], np.float32))
+    return cfg, synth.finish_triangles(a)
+
+
+def test_deep_recursion_fits_the_continuation_stack():
+    """rt_render sizes the per-sample continuation stack from `bounces` and `gi` (render.cu, P.depth) and reports an
+    overflow as an error; the reference has no such limit (it recurses on a 64 KiB stack, main.cu:64), so a scene the
+    reference renders must never overflow here.  Worst-case materials at bounces 4 and 8 against the oracle's own
+    recursion (ids, image, ray count), and at bounces 16 (tenthousand.txt's value) and with GI on top: no error, and the
+    same image in the exact and the reference-order lane."""
+    for bounces, gi in ((4, 0), (8, 0), (5, 3)):
+        cfg, a = hall_of_mirrors(bounces, gi)
+        o = H.oracle_from_arrays(cfg, a)
+        sc = built_pair(o)
+        g, r = compare_render(o, sc, 16, 12, 0)
+        assert g["counters"].rays > 16 * 12 * 3 * bounces, "the scene does not branch as intended: %d rays" % g["counters"].rays
+        compare_render(o, sc, 6, 4, 32 if bounces <= 5 else 0)
+        sc.close()
+    for bounces, gi in ((16, 0), (12, 2)):   # ~90 000 rays per pixel at bounces 16: a handful of pixels
+        cfg, a = hall_of_mirrors(bounces, gi)
+        o = H.oracle_from_arrays(cfg, a)
+        sc = built_pair(o)
+        g, r = compare_render(o, sc, 6, 4, 0)            # an overflow would raise RtError
+        a1 = sc.render(6, 4, 0, api.TRAVERSE_REF_ORDER, want_ids=True)
+        assert np.array_equal(g["rgba"], a1["rgba"]) and g["counters"].rays == a1["counters"].rays
+        print("bounces %d gi %d: %d rays for 24 pixels, %d wavefront iterations" % (bounces, gi, g["counters"].rays, g["counters"].wavefront_iters))
+        assert g["counters"].rays > 24 * 5000
+        sc.close()
