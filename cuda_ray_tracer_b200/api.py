@@ -65,7 +65,7 @@ EXPORTS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_update_triangles", "
            "rt_png_read", "rt_free", "rt_xorwow_init", "rt_last_error", "rt_version",
            "rt_comm_init", "rt_comm_unique_id", "rt_comm_init_rank", "rt_comm_destroy", "rt_comm_size", "rt_comm_num_local", "rt_comm_local_rank",
            "rt_comm_local_device", "rt_tile_shape", "rt_scene_broadcast", "rt_comm_update_triangles", "rt_comm_build_lbvh", "rt_framebuffer_gather",
-           "rt_render_multi", "rt_render_reserve", "rt_device_alloc", "rt_device_free"]
+           "rt_render_multi", "rt_render_reserve", "rt_device_alloc", "rt_device_free", "rt_trace_static", "rt_trace_static_max_rays"]
 
 
 def load_library():
@@ -115,6 +115,8 @@ def load_library():
     L.rt_comm_build_lbvh.argtypes = [vp, pvp, ip, C.c_uint, C.POINTER(C.c_float)]
     L.rt_framebuffer_gather.argtypes = [vp, pvp, ip, ip, ip, ip, ip, pvp]
     L.rt_render_reserve.argtypes = [vp, ip, ip]
+    L.rt_trace_static.argtypes = [vp, ip, vp, vp, C.c_uint, vp, vp, vp]
+    L.rt_trace_static_max_rays.argtypes = []
     L.rt_device_alloc.argtypes = [ip, C.c_size_t]; L.rt_device_alloc.restype = vp
     L.rt_device_free.argtypes = [ip, vp]; L.rt_device_free.restype = None
     L.rt_render_multi.argtypes = [vp, pvp, ip, ip, ip, C.c_uint, ip, ip, ip, pvp, vp, C.POINTER(Counters)]
@@ -291,6 +293,10 @@ class Scene:
     def trace_device(self, n, d_org, d_dir, d_ids, d_t=None, flags=0, counters=None, stream=None):
         _check(load_library().rt_trace(self.h, n, _ptr(d_org), _ptr(d_dir), flags, _ptr(d_ids), _ptr(d_t),
                                        C.byref(counters) if counters is not None else None, stream), "rt_trace")
+
+    def trace_static(self, n, d_org, d_dir, d_ids, d_t=None, flags=0, stream=None):
+        """rt_trace_static: rt_trace with its scratch in a fixed device array (no allocation; n <= rt_trace_static_max_rays())"""
+        _check(load_library().rt_trace_static(self.h, n, _ptr(d_org), _ptr(d_dir), flags, _ptr(d_ids), _ptr(d_t), stream), "rt_trace_static")
 
 
 def triangle_setup(p0, p1, p2):

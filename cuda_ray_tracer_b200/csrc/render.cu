@@ -1418,3 +1418,75 @@ extern "C" int rt_trace(rt_scene* s, int n, const float* d_org, const float* d_d
   }
   return RT_OK;
 }
+
+// ---- rt_trace_static: rt_trace for callers that must not allocate ---------------------------------------------------
+// No counterpart in the reference.  Some callers cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  rt_trace keeps its scratch — the
+// packed ray queue (32 B per ray), the hit records (8 B), the exact lane's fallback list (4 B), fetch tickets — in
+// buffers it cudaMallocs on demand.  This variant keeps the same scratch in ONE file-scope device array of fixed size,
+// so the call allocates nothing: no cudaMalloc / cudaFree / cudaMallocHost, no events, no library routine that allocates.
+//   * limit: RT_TRACE_STATIC_MAX_RAYS rays per call (131072 => 5.5 MiB); more is rejected with RT_ERR_INVALID.  Every GPU
+//     that loads libb200rt.so holds the array until the process exits.
+//   * the array is shared by every call on the device and keeps the last call's contents: the tickets / fallback count
+//     are cleared at the start of each call (cudaMemsetAsync on the caller's stream), everything else is overwritten
+//     before it is read.  Calls that OVERLAP on the GPU (two streams, two host threads) race on it: serialise them.
+//   * in host code `g_trace_scratch` is a host-side stand-in, not a device address: the address the kernels get is
+//     fetched once per device, with that device current, by cudaGetSymbolAddress.
+#define RT_TRACE_STATIC_MAX_RAYS 131072
+#define RT_TRACE_STATIC_HEADER 512   /* 64 counter words + 32 stats words */
+static __device__ __align__(256) unsigned char g_trace_scratch[RT_TRACE_STATIC_HEADER + (size_t)RT_TRACE_STATIC_MAX_RAYS * (32 + 8 + 4)];
+
+namespace {
+struct StaticTraceDev { unsigned char* scratch = nullptr; int grid = 0; };
+std::mutex g_static_trace_mu;
+StaticTraceDev g_static_trace[64];
+
+int static_trace_setup(int device, StaticTraceDev& out) {  // the caller made `device` current
+  if (device < 0 || device >= 64) { rt_set_error("rt_trace_static: device index out of range"); return RT_ERR_INVALID; }
+  std::lock_guard<std::mutex> lk(g_static_trace_mu);
+  StaticTraceDev& d = g_static_trace[device];
+  if (!d.scratch) {
+    void* p = nullptr;
+    RT_CUDA(cudaGetSymbolAddress(&p, g_trace_scratch));
+    int per_sm = 0, sms = 0;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse_near_kernel<true, false, false, false>, RT_TRAV_THREADS, 0));
+    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    d.grid = sms * (per_sm < 1 ? 1 : per_sm);
+    d.scratch = (unsigned char*)p;
+  }
+  out = d;
+  return RT_OK;
+}
+}  // namespace
+
+extern "C" int rt_trace_static_max_rays(void) { return RT_TRACE_STATIC_MAX_RAYS; }
+
+extern "C" int rt_trace_static(rt_scene* s, int n, const float* d_org, const float* d_dir, unsigned flags, int32_t* d_hit_id, float* d_hit_t,
+                               void* stream) {
+  if (!s || !d_org || !d_dir || !d_hit_id || n < 0) { rt_set_error("rt_trace_static: bad argument"); return RT_ERR_INVALID; }
+  if (n > RT_TRACE_STATIC_MAX_RAYS) {
+    rt_set_error("rt_trace_static: " + std::to_string(n) + " rays exceed the static scratch (RT_TRACE_STATIC_MAX_RAYS = " +
+                 std::to_string(RT_TRACE_STATIC_MAX_RAYS) + "); split the batch or use rt_trace");
+    return RT_ERR_INVALID;
+  }
+  if (s->n > 0 && !s->built) { rt_set_error("rt_trace_static: rt_build_lbvh has not run"); return RT_ERR_NOT_BUILT; }
+  RT_CUDA(cudaSetDevice(s->device));
+  StaticTraceDev dev;
+  const int rc = static_trace_setup(s->device, dev);
+  if (rc) return rc;
+  if (n == 0) return RT_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  uint32_t* ctr = (uint32_t*)dev.scratch;
+  unsigned long long* stats = (unsigned long long*)(dev.scratch + 256);
+  float4* q = (float4*)(dev.scratch + RT_TRACE_STATIC_HEADER);
+  float2* hits = (float2*)(dev.scratch + RT_TRACE_STATIC_HEADER + (size_t)RT_TRACE_STATIC_MAX_RAYS * 32);
+  unsigned* fb = (unsigned*)(dev.scratch + RT_TRACE_STATIC_HEADER + (size_t)RT_TRACE_STATIC_MAX_RAYS * 40);
+  const RtDeviceScene sc = device_scene(s);
+  RT_CUDA(cudaMemsetAsync(dev.scratch, 0, RT_TRACE_STATIC_HEADER, st));  // tickets, fallback count, stats: must start at zero
+  pack_rays_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_org, d_dir, n, q);
+  launch_traverse(lane_of(flags), false, dev.grid, st, sc, (const float4*)q, (unsigned)n, 0u, (unsigned)n, hits, ctr, stats, fb, nullptr,
+                  (flags & RT_TRAVERSE_PACKET) != 0);
+  unpack_hits_kernel<<<(n + 255) / 256, 256, 0, st>>>(hits, s->sorted_perm, n, d_hit_id, d_hit_t);
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}

@@ -167,6 +167,17 @@ int rt_render_reserve(rt_scene* scene, int w, int h);
 int rt_trace(rt_scene* scene, int n, const float* d_org, const float* d_dir, unsigned flags,
              int32_t* d_hit_id, float* d_hit_t, rt_counters* counters, void* stream);
 
+/* rt_trace without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs,
+ * outputs, flags (lane selection) and results as rt_trace, asynchronous on `stream`; its scratch (packed rays, hit
+ * records, fallback list, tickets) lives in one file-scope device array of fixed size instead of buffers allocated on
+ * demand, so the call performs no cudaMalloc / cudaFree / host allocation of CUDA memory.  Limit: n <=
+ * rt_trace_static_max_rays() (131072 rays, 5.5 MiB held by every GPU that loads the library until exit); larger n
+ * returns RT_ERR_INVALID.  All calls on a device share the array: calls that overlap on the GPU race — serialise them. */
+int rt_trace_static(rt_scene* scene, int n, const float* d_org, const float* d_dir, unsigned flags,
+                    int32_t* d_hit_id, float* d_hit_t, void* stream);
+int rt_trace_static_max_rays(void);
+
 /* ---- multi-GPU -------------------------------------------------------------------
  * No counterpart in the reference: it is a single-GPU program (main.cu:25-94, job.slurm:7-11).  The
  * path shards by image tiles: the scene is replicated, every GPU builds the same LBVH itself and
