@@ -23,6 +23,9 @@
 
 #include "../../include/rt_api.h"
 
+#ifndef RT_INLINE_SUN
+#define RT_INLINE_SUN 0   // experiment: inline sun shadow rays (traverse.cuh)
+#endif
 #define RT_TV_STRIDE 6  // float4 words per sorted leaf record (96 bytes = three 32-byte sectors)
 // File-order primitive records: 48 bytes (three float4) per primitive in each of the two views.
 // (Measured and rejected, profiles/build_ab_r02.txt: ONE interleaved 128-byte record per primitive, so that the builder's

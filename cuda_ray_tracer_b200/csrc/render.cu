@@ -643,6 +643,62 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
   }
 }
 
+// ---- shade, inline-sun passes ---------------------------------------------------------------------------------------
+// Scenes without mirrors, glass, GI or rough surfaces, lit by one sun: a sample is its primary ray and, if that hits, one
+// shadow ray, which traverse_near_kernel traces inline (hits2 / `occl`).  One visit per sample then does what
+// shade_kernel<false, true> and shade_kernel<false, false> do in two, with the same expressions in the same order
+// (shootPrimaryRay draw.cu:269-282, diffuseLight :329-353, getColorSun :627-647): no continuation frame, no second
+// queue.  The number of shadow rays (= hits) is added to counters[5], where the accounting expects the next iteration's rays.
+__global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_inline_kernel(const RenderParams P, const RtDeviceScene sc, const RenderBuffers B,
+                                                                             const float4* __restrict__ qin, const unsigned* __restrict__ occl,
+                                                                             int32_t* __restrict__ hit_id_out, const unsigned* __restrict__ counts_dev) {
+  const unsigned n = counts_dev[1];
+  for (unsigned g0 = blockIdx.x * blockDim.x; g0 < n; g0 += gridDim.x * blockDim.x) {  // block-uniform
+    const unsigned r = g0 + threadIdx.x;
+    bool shaded = false;
+    float4 q1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(RT_RAY_DEAD));
+    if (r < n) q1 = __ldcs(qin + 2 * (size_t)r + 1);
+    if (__float_as_uint(q1.w) != RT_RAY_DEAD) {
+      const float4 q0 = __ldcs(qin + 2 * (size_t)r);
+      const float2 hv = __ldcs(B.hits + r);
+      const V3 o = mk3(q0.x, q0.y, q0.z), d = mk3(q1.x, q1.y, q1.z);
+      const int i = (int)__float_as_uint(q1.w);
+      const float ht = hv.x; const int hid = __float_as_int(hv.y);
+      if (hit_id_out) {
+        const int lp = i / P.spp;
+        if (i - lp * P.spp == 0) {
+          int x, y, pix; slot_to_pixel(P, P.slot0 + lp, x, y, pix);
+          int out_id = hid;
+          if (hid >= 0) out_id = (int)__ldg(sc.perm + ((unsigned)hid & RT_LEAF_MASK));
+          hit_id_out[pix] = out_id;
+        }
+      }
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (hid != -1) {
+        SurfHit h; reconstruct_hit(sc, hid, ht, o, d, h);
+        acc.w = 1.0f;  // color.a = 1, draw.cu:281
+        shaded = true;
+        if (__ldcs(occl + r) == 0u) {
+          const V3 one = mk3(1.0f, 1.0f, 1.0f);
+          const V3 Wt = mk3(1.f, 1.f, 1.f);
+          const V3 ms = one - h.shin;
+          const V3 df_w = mul3(Wt, mul3(ms, one - h.trans));
+          const V3 df_nrm = normalize3(h.normal);
+          const LightSun& L = sc.suns[0];
+          const V3 ldir = mk3(L.dir[0], L.dir[1], L.dir[2]), lcol = mk3(L.color[0], L.color[1], L.color[2]);
+          const float lambert = fmax(dot(df_nrm, normalize3(ldir)), 0.0f);
+          const float cr = h.color.x * (lcol.x * lambert), cg = h.color.y * (lcol.y * lambert), cb = h.color.z * (lcol.z * lambert);
+          const float er = set_expose(cr, P.cam.expose), eg = set_expose(cg, P.cam.expose), eb = set_expose(cb, P.cam.expose);
+          acc.x += df_w.x * er; acc.y += df_w.y * eg; acc.z += df_w.z * eb;
+        }
+      }
+      B.accum[i] = acc;
+    }
+    const int nshaded = __syncthreads_count(shaded);  // one atomic per block: a single hot counter serialises in L2
+    if (nshaded && threadIdx.x == 0) { atomicAdd(B.stats + 2, (unsigned long long)nshaded); atomicAdd(B.counters + 5, (unsigned)nshaded); }
+  }
+}
+
 // ---- resolve: sample sum in the butterfly order of render_kernel_warp_aa, sRGB, 8-bit store -----
 __device__ __forceinline__ float rgb_to_srgb(float l) {  // RGBtosRGB, helper.cu:12-27
   float sol;
@@ -822,13 +878,14 @@ int lane_of(unsigned flags) {
 // ctr: [0] fetch ticket front, [3] fallback count, [4] fallback fetch ticket, [6] fetch ticket back.
 template <bool EXACT, bool WIDE>
 void launch_near_w(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
-                   float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
+                   float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back,
+                   unsigned* hits2) {
   if (sun) {
-    if (count) traverse_near_kernel<EXACT, true, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
-    else traverse_near_kernel<EXACT, false, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    if (count) traverse_near_kernel<EXACT, true, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, nullptr);
+    else traverse_near_kernel<EXACT, false, true, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, nullptr);
   } else {
-    if (count) traverse_near_kernel<EXACT, true, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
-    else traverse_near_kernel<EXACT, false, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    if (count) traverse_near_kernel<EXACT, true, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, hits2);
+    else traverse_near_kernel<EXACT, false, false, WIDE><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, hits2);
   }
 }
 // the packet kernel's persistent grid: every SM full
@@ -862,7 +919,8 @@ void launch_packet(bool count, bool sun, long long n_hint, cudaStream_t st, cons
 }
 template <bool EXACT>
 void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned first, unsigned n,
-                 float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back) {
+                 float2* hits, unsigned* fetch, unsigned long long* stats, unsigned* fb_list, unsigned* fb_count, const unsigned* n_dev, unsigned cap_back,
+                 unsigned* hits2) {
   if (sc.wnodes && sc.n > 1) {
     static int wide_per_sm[2] = {0, 0};  // the wide kernels hold more registers: fewer resident CTAs, hence a smaller persistent grid
     int& w = wide_per_sm[sun ? 1 : 0];
@@ -873,9 +931,9 @@ void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDevice
     }
     int sms = 148; { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     grid = std::min(grid, sms * w);
-    launch_near_w<EXACT, true>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+    launch_near_w<EXACT, true>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, hits2);
   }
-  else launch_near_w<EXACT, false>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back);
+  else launch_near_w<EXACT, false>(count, sun, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, fb_count, n_dev, cap_back, hits2);
 }
 // counts_dev == nullptr: nf / nb are the ray counts (the host read them back).  counts_dev != nullptr (a pass queued without host
 // round trips): the kernels read the counts from counts_dev[1] (front) and counts_dev[5] (back); nf / nb only say which
@@ -884,7 +942,7 @@ void launch_near(bool count, bool sun, int grid, cudaStream_t st, const RtDevice
 // walks the tree once for 32 consecutive rays (traverse_packet_kernel) instead of 32 independent lanes
 int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const RtDeviceScene& sc, const float4* rays, unsigned nf, unsigned nb,
                     unsigned cap, float2* hits, unsigned* ctr, unsigned long long* stats, unsigned* fb_list, const unsigned* counts_dev = nullptr,
-                    bool packet = false) {
+                    bool packet = false, unsigned* hits2 = nullptr) {  // hits2: inline sun shadow rays (near-first lanes, front end only)
   int launches = 0;
   for (int end = 0; end < 2; end++) {
     const unsigned n = end ? nb : nf, first = end ? cap - nb : 0u;
@@ -894,20 +952,20 @@ int launch_traverse(int lane, bool count, int max_grid, cudaStream_t st, const R
     const unsigned cap_back = (counts_dev && end) ? cap : 0u;
     const int grid = counts_dev ? max_grid : (int)std::min<long long>(max_grid, ((long long)n + RT_TRAV_THREADS - 1) / RT_TRAV_THREADS);
     if (lane == RT_LANE_REF) {
-      if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
-      else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back);
+      if (count) traverse_ref_kernel<true><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back, nullptr);
+      else traverse_ref_kernel<false><<<grid, RT_TRAV_THREADS, 0, st>>>(sc, rays, first, n, hits, fetch, stats, nullptr, nullptr, n_dev, cap_back, nullptr);
     } else if (packet && sc.n > 0) {
       const long long n_hint = counts_dev ? -1ll : (long long)n;
       if (lane == RT_LANE_NEAR) launch_packet<false>(count, end == 1, n_hint, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
       else launch_packet<true>(count, end == 1, n_hint, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
-    } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
-    else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back);
+    } else if (lane == RT_LANE_NEAR) launch_near<false>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back, end == 0 ? hits2 : nullptr);
+    else launch_near<true>(count, end == 1, grid, st, sc, rays, first, n, hits, fetch, stats, fb_list, ctr + 3, n_dev, cap_back, end == 0 ? hits2 : nullptr);
     launches++;
   }
   if (lane == RT_LANE_EXACT && nf + nb > 0) {
     const int g2 = max_grid < 148 ? max_grid : 148;
-    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u);
-    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u);
+    if (count) traverse_ref_kernel<true><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u, hits2);
+    else traverse_ref_kernel<false><<<g2, RT_TRAV_THREADS, 0, st>>>(sc, rays, 0u, 0u, hits, ctr + 4, stats, fb_list, ctr + 3, nullptr, 0u, hits2);
     launches++;
   }
   return launches;
@@ -1229,6 +1287,10 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   const long long npasses_total = npix_pass > 0 ? (nslots + npix_pass - 1) / npix_pass : 0;
   // (a lambda: RT_CUDA returns from IT, so a failure inside lands in the common error path below, which waits for the
   // kernels already queued on the pass and head streams before the call returns — as the host-driven loop does)
+  // inline sun shadow rays (traverse.cuh): one traverse launch and one shade visit per pass
+  // (experiment build only, -DRT_INLINE_SUN=1: measured slower than the two specialised launches, traverse.cuh)
+  const bool inline_sun = RT_INLINE_SUN && queued && nl == 1 && s->cfg.num_suns == 1 && !s->any_rough && P.ref_order != RT_LANE_REF && pkt_mode == 0 &&
+                          getenv("RT_NO_INLINE_SUN") == nullptr;
   auto run_queued = [&]() -> int {
     const size_t words = (size_t)npasses_total * 256;
     if (words > rs->h_blocks_words) {
@@ -1263,6 +1325,21 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
       }
       float4 *qin = c.B.qa, *qout = c.B.qb;
       const unsigned sgrid = (unsigned)std::min<long long>(((long long)c.P.S + 127) / 128, (long long)sms * RT_SHADE_MIN_CTAS * 4);
+      if (inline_sun) {
+        uint32_t* blk = c.counters;
+        unsigned* occl = (unsigned*)c.B.qb;  // the second queue is not used by these passes: one word per slot
+        if (time_trav) RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1))], c.st));
+        const int tl = launch_traverse(P.ref_order, count, rs->trav_grid, c.st, sc, (const float4*)qin, 1u, 0u, (unsigned)c.P.S, c.B.hits,
+                                       blk, rs->stats, c.B.fb_list, blk, false, occl);
+        launches += tl; trav_launches += tl - (P.ref_order == RT_LANE_EXACT ? 1 : 0);
+        if (time_trav) {
+          RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1)) + 1], c.st));
+          RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + 1)], c.st)); RT_CUDA(cudaEventRecord(rs->ev_pool[2 * (pi * (nl + 1) + 1) + 1], c.st));  // no second iteration
+        }
+        RenderBuffers Bn = c.B; Bn.counters = blk + 16;
+        shade_inline_kernel<<<sgrid, 128, 0, c.st>>>(c.P, sc, Bn, qin, occl, d_hit_id, blk);
+        launches++;
+      } else
       for (int it = 0; it <= nl; it++) {
         uint32_t* blk = c.counters + 16 * it;
         // which queue ends can hold rays: primary rays go to the front; shadow rays to a sun go to the back, to a bulb to the front

@@ -11,7 +11,7 @@
 static thread_local std::string g_err;
 void rt_set_error(const std::string& msg) { g_err = msg; }
 extern "C" const char* rt_last_error(void) { return g_err.c_str(); }
-extern "C" const char* rt_version(void) { return "b200rt 0.1 (sm_100a)"; }
+extern "C" const char* rt_version(void) { return RT_INLINE_SUN ? "b200rt 0.2 (sm_100a) inline-sun" : "b200rt 0.2 (sm_100a)"; }
 
 namespace {
 

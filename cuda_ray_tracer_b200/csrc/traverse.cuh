@@ -231,6 +231,40 @@ __device__ __forceinline__ RtHit rt_finish_with_planes(const RtDeviceScene& sc, 
   return h;
 }
 
+// Hit point and facing normal of hit `id` at distance t along (o, d): the ObjectInfo fields the reference's intersection
+// routines return (struct.cu:76-108 sphere, :124,160 triangle; draw.cu:597-611 plane).  The same expressions as
+// reconstruct_hit (render.cu), so that a shadow ray generated here starts where the shade kernel would start it.
+__device__ __forceinline__ void rt_hit_point_normal(const RtDeviceScene& sc, const int id, const float t, const V3 o, const V3 d, V3& point, V3& normal) {
+  point = t * d + o;
+  if (id >= 0) {
+    const unsigned k = (unsigned)id & RT_LEAF_MASK;
+    const float4 a = __ldg(sc.sorted_tv + RT_TV_STRIDE * (size_t)k);
+    if ((unsigned)id & RT_SPHERE_BIT) {
+      const V3 c = mk3(a.x, a.y, a.z);
+      const V3 cr0 = c - o;
+      const bool inside = dot(cr0, cr0) < a.w * a.w;
+      normal = normalize3(inside ? (c - point) : (point - c));
+    } else {
+      const float4 b = __ldg(sc.sorted_tv + RT_TV_STRIDE * (size_t)k + 1);
+      const V3 nor = mk3(a.w, b.x, b.y);
+      normal = (dot(d, nor) < 0.0f) ? nor : -nor;
+    }
+  } else {
+    const float* pl = reinterpret_cast<const float*>(sc.planes + (-2 - id));
+    const V3 nor = mk3(__ldg(pl), __ldg(pl + 1), __ldg(pl + 2));
+    normal = (dot(nor, d) < 0.0f) ? nor : -nor;
+  }
+}
+// origin and direction of the shadow ray towards sun 0 from that hit (diffuseLight, draw.cu:329-353: origin offset by
+// the unperturbed normal * 1e-3, Ray(eye, dir, 1) normalises the direction, object.cuh:69)
+__device__ __forceinline__ void rt_sun_shadow_ray(const RtDeviceScene& sc, const int id, const float t, const V3 o, const V3 d, V3& so, V3& sd) {
+  V3 pt, nrm;
+  rt_hit_point_normal(sc, id, t, o, d, pt, nrm);
+  so = pt + nrm * 0.001f;
+  const LightSun& L = sc.suns[0];
+  sd = normalize3(mk3(L.dir[0], L.dir[1], L.dir[2]));
+}
+
 // ---- RT_LANE_REF: traverse_lbvh's own loop (bvh_traversal.cu:92-183) over the 64-byte nodes ----------------
 // anyhit: shadow ray — only "is there a hit closer than tlimit" is wanted (the reference runs a closest-hit
 // search and looks at isHit / distance < |bulbDir|, draw.cu:348-367); tmax still evolves from +INF.
@@ -306,7 +340,10 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
                                                                       const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                       unsigned long long* stats, const unsigned* __restrict__ list,
                                                                       const unsigned* __restrict__ list_count,
-                                                                      const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+                                                                      const unsigned* __restrict__ n_dev, const unsigned cap_back,
+                                                                      unsigned* __restrict__ hits2) {
+  // hits2 != nullptr (inline sun shadow rays, see traverse_near_kernel): a ray that hits something is followed by its
+  // shadow ray towards sun 0, traced here in the same order; hits2[r] = 1 when that ray is occluded
   // n_dev != nullptr: the ray count is read on the device (a pass queued without host round trips, render.cu);
   // cap_back != 0: the rays are the back end of the queue, slots [cap_back - n, cap_back)
   const unsigned n = n_dev ? *n_dev : n_in, first = (n_dev && cap_back) ? cap_back - n : first_in;
@@ -328,6 +365,15 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
         const RtHit h = rt_trace_ref<COUNT>(sc, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), q0.w,
                                             (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u, S, n_nodes, n_leaves);
         __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+        if (hits2) {
+          unsigned occ = 0u;
+          if (h.id != -1) {
+            V3 so, sd;
+            rt_sun_shadow_ray(sc, h.id, h.t, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), so, sd);
+            occ = rt_trace_ref<COUNT>(sc, so, sd, INFINITY, true, S, n_nodes, n_leaves).id != -1 ? 1u : 0u;
+          }
+          __stcs(hits2 + r, occ);
+        }
       }
     }
     __syncwarp();
@@ -356,14 +402,24 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS) traverse_ref_kernel(const RtD
 // SUN: the queue end that holds only sun shadow rays (any hit, no distance limit).  Their answer is "does a
 // candidate exist", whatever the order, so this instantiation carries no culling keys at all: the exact box test
 // decides, the stack holds references only, a pop is a pop.
+// EXPERIMENT, off by default (-DRT_INLINE_SUN=1): trace the sun shadow ray INLINE in the lane that has just found a primary
+// hit (see the hits2 comment in traverse_near_kernel).  Bit-identical images (tests/test_render_gpu.py::
+// test_inline_sun_passes_equal_two_launch_passes), one traverse launch and one drain per pass instead of two — and slower:
+// 3801 vs 4107 Mrays/s on the 4K frame, 6.42 vs 6.23 ms for one rank's step of the 8-GPU frame (profiles/inline_sun_r02.txt).
+// The fused launch takes 19.6 ms where the two launches take 10.6 + 6.4: the shadow rays lose the key-free SUN
+// instantiation (4-byte stack entries, no culling keys) and, mixed into the same warps, dilute the coherence the
+// pixel-major queue gives the primary rays.
+#ifndef RT_INLINE_SUN
+#define RT_INLINE_SUN 0
+#endif
 #ifndef RT_TRAV_MIN_CTAS
-#define RT_TRAV_MIN_CTAS 1
+#define RT_TRAV_MIN_CTAS (RT_INLINE_SUN ? 9 : 1)   // the inline-sun experiment takes the kernel from 56 to 62 registers unless it is held to 9 CTAs per SM (55, no spills)
 #endif
 #ifndef RT_WIDE_MIN_CTAS
 #define RT_WIDE_MIN_CTAS 9   // 4-wide instantiations (experimental): resident CTAs per SM the compiler must allow (56 registers; measured
                              // 3445 Mrays/s against 3397 at 8 CTAs / 64 registers and 3325 at 7 / 70)
 #endif
-enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u };  // per-ray flags of the near-first kernels
+enum : unsigned { F_ANYHIT = 1u, F_WANTKEY = 2u, F_FALLBACK = 4u, F_INCONS = 8u, F_SHADOW = 16u /* the inline sun shadow ray of slot r */ };  // per-ray flags of the near-first kernels
 // Certificate of the exact lane (closest-hit rays).  The winner m = (t*, k*) is the reference's answer when every
 // box on its path is entered before the reference's running tmax at that moment.  Entry distances grow down a
 // path, so that is implied by e_m < t* (e_m = entry of m's own leaf box; "consistent").  When e_m >= t* (the hit
@@ -412,7 +468,13 @@ template <bool EXACT, bool COUNT, bool SUN, bool WIDE>
 __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_TRAV_MIN_CTAS) traverse_near_kernel(const RtDeviceScene sc, const float4* __restrict__ rays, const unsigned first_in,
                                                                        const unsigned n_in, float2* __restrict__ hits, unsigned* fetch_counter,
                                                                        unsigned long long* stats, unsigned* __restrict__ fb_list,
-                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back) {
+                                                                       unsigned* fb_count, const unsigned* __restrict__ n_dev, const unsigned cap_back,
+                                                                       unsigned* __restrict__ hits2) {
+  // hits2 != nullptr: INLINE SUN SHADOW RAYS (scenes without mirrors, glass, GI or rough surfaces, lit by one sun).  The lane
+  // that has just finished a primary ray with a hit writes the hit, builds the shadow ray towards the sun from it and
+  // traces it at once (an any-hit ray without a distance limit: tcull stays +INF, nothing is culled, no certificate);
+  // hits2[r] = 1 when it is occluded.  A frame is then ONE traverse launch per pass instead of two: one drain of long
+  // rays instead of two, and the shadow rays never travel through HBM as queue records (render.cu, shade_inline_kernel).
   // the two values are needed once per chunk of rays: kept in shared memory, not in two registers of every thread
   // (56 registers = 9 CTAs per SM; 59 = 8)
   constexpr bool LEAF_BOX_FIRST = WIDE && RT_WIDE_BF16;
@@ -455,14 +517,36 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
     // ---- retire finished rays and refill from the warp's chunk, RT_REFILL_MIN lanes at a time ----
     const unsigned free_m = ~actm;
     if (free_m && (__popc(free_m) >= RT_REFILL_MIN || actm == 0u)) {
+      unsigned idle_m = free_m;  // lanes that can take a new ray
       if (st == DONE) {
-        if (EXACT && ((fl & F_FALLBACK) || ((fl & F_INCONS) && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;
+        st = IDLE;
+        if (EXACT && ((fl & F_FALLBACK) || ((fl & F_INCONS) && !(t2 > tcull)))) fb_list[atomicAdd(fb_count, 1u)] = r;  // (inline mode: the reference-order pass redoes ray AND shadow ray)
         else {
           const RtHit h = rt_finish_with_planes(sc, rt_ray2_o(q2), d, tlimit, SUN || (fl & F_ANYHIT), tmax, best);
-          __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+          if (RT_INLINE_SUN && !SUN && hits2 && (fl & F_SHADOW)) __stcs(hits2 + r, h.id != -1 ? 1u : 0u);
+          else {
+            __stcs(hits + r, make_float2(h.t, __int_as_float(h.id)));
+            if (RT_INLINE_SUN && !SUN && hits2) {
+              if (h.id != -1 && sc.n == 0) {  // planes only: nothing to traverse
+                V3 so, sd;
+                rt_sun_shadow_ray(sc, h.id, h.t, rt_ray2_o(q2), d, so, sd);
+                __stcs(hits2 + r, rt_finish_with_planes(sc, so, sd, INFINITY, true, INFINITY, -1).id != -1 ? 1u : 0u);
+              } else if (h.id != -1) {  // this lane goes on with the shadow ray of its hit
+                V3 so, sd;
+                rt_sun_shadow_ray(sc, h.id, h.t, rt_ray2_o(q2), d, so, sd);
+                d = sd; tlimit = INFINITY;
+                const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                omk = (RT_ORIGIN_SLACK * 1.000001f) * fmaxf(fmaxf(fabsf(so.x), fabsf(so.y)), fabsf(so.z));
+                q2 = rt_ray2(so, inv);
+                tmax = INFINITY; tcull = INFINITY; tcut = INFINITY; t2 = INFINITY; best = -1; sp = 0; cur = (unsigned)__ldg(sc.root);
+                fl = F_ANYHIT | F_SHADOW;
+                st = ACTIVE;
+              } else __stcs(hits2 + r, 0u);
+            }
+          }
         }
-        st = IDLE;
       }
+      if (RT_INLINE_SUN && !SUN && hits2) idle_m = __ballot_sync(0xffffffffu, st == IDLE);  // converted lanes are busy again
       if (!exhausted) {
         if (chunk_next == chunk_end) {
           // (Guided chunk sizes — ever smaller pieces towards the end of the queue — were measured: no change of the
@@ -475,8 +559,8 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
           else { chunk_next = first + base; chunk_end = first + min(base + (unsigned)RT_CHUNK, n); }
         }
         if (!exhausted) {
-          const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(free_m);
-          const unsigned take = min(avail, want), rank = (unsigned)__popc(free_m & ((1u << lane) - 1u));
+          const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(idle_m);
+          const unsigned take = min(avail, want), rank = (unsigned)__popc(idle_m & ((1u << lane) - 1u));
           bool fetch = st == IDLE && rank < take;
           float4 q1 = make_float4(0.f, 0.f, 0.f, 0.f);
           if (fetch) { r = chunk_next + rank; q1 = __ldcs(rays + 2 * (size_t)r + 1); fetch = __float_as_uint(q1.w) != RT_RAY_DEAD; }  // DEAD: no ray in this slot

@@ -649,3 +649,77 @@ def test_deep_recursion_fits_the_continuation_stack():
         print("bounces %d gi %d: %d rays for 24 pixels, %d wavefront iterations" % (bounces, gi, g["counters"].rays, g["counters"].wavefront_iters))
         assert g["counters"].rays > 24 * 5000
         sc.close()
+
+
+def test_inline_sun_passes_equal_two_launch_passes(monkeypatch):
+    """EXPERIMENT BUILD (make EXTRA=-DRT_INLINE_SUN=1; measured slower, off by default — with the default library this test
+    compares the standard schedules with each other).  Scenes without mirrors, glass, GI or rough surfaces lit by one sun take
+    the inline-sun passes (the lane that finds a
+    primary hit traces its shadow ray at once; one traverse launch and one shade visit per pass).  Same bytes, ids and ray
+    counts as the two-launch passes (RT_NO_INLINE_SUN), the host-driven loop and the reference-order lane: triangle soup,
+    sphere field, mixed scene with a plane (plane hits and plane occluders), slivers (rays that fail the certificate go
+    through the reference-order pass, which then traces ray AND shadow ray), a planes-only scene, tiny trees; 1 spp and
+    multi-sample, many small passes, interleaved tiles, exposure."""
+    scenes = []
+    cfg, a = synth.soup(60_000, seed=4, width=200, height=120, aa=4)
+    scenes.append(H.oracle_from_arrays(cfg, synth.finish_triangles(a)))
+    cfg, a = synth.spheres(40_000, seed=5, width=200, height=120, aa=4)
+    scenes.append(H.oracle_from_arrays(cfg, a))
+    cfg, a = H.mixed_scene(5000)
+    a["planes"] = np.array([[0, 1, 0, 1.2] + [0, 1, 0] + [0, -1.2, 0] + [0.5, 0.5, 0.5, 0, 0, 0, 0, 0, 0, 1.458, 0]], np.float32)
+    a["suns"] = np.array([[0.3, 1, 0.4, 1, 0.9, 0.8]], np.float32)
+    cfg["expose"] = 1.7
+    scenes.append(H.oracle_from_arrays(cfg, a))
+    cfg, a = sliver_scene(6000, 8)
+    a["bulbs"] = np.zeros((0, 6), np.float32)
+    scenes.append(H.oracle_from_arrays(cfg, a))
+    for n in (1, 2, 3):
+        cfg, a = synth.soup(n, seed=n, width=32, height=32, aa=0)
+        scenes.append(H.oracle_from_arrays(cfg, synth.finish_triangles(a)))
+    fallbacks = 0
+    for o in scenes:
+        for aa, fl, (w, h), tiles, pool in ((0, 0, (200, 120), None, None), (6, api.SPP_TRUE, (100, 60), None, 300_000), (32, 0, (48, 32), api.TileSet(32, 8, 3, 2), None)):
+            ref = None
+            for no_inline, host_driven, lane in ((True, False, api.TRAVERSE_REF_ORDER), (False, False, 0), (True, False, 0), (False, True, 0), (False, False, api.TRAVERSE_NEAR_FIRST),
+                                                 (True, False, api.TRAVERSE_NEAR_FIRST)):
+                for k, v in (("RT_NO_INLINE_SUN", no_inline), ("RT_HOST_DRIVEN", host_driven)):
+                    if v: monkeypatch.setenv(k, "1")
+                    else: monkeypatch.delenv(k, raising=False)
+                if pool is None: monkeypatch.delenv("RT_POOL_BYTES", raising=False)
+                else: monkeypatch.setenv("RT_POOL_BYTES", str(pool))
+                sc = built_pair(o)
+                r = sc.render(w, h, aa, fl | lane | api.COUNTERS, tiles=tiles, want_ids=True, want_written=True)
+                sc.close()
+                if lane == api.TRAVERSE_NEAR_FIRST:   # plain near-first: compare its two schedules with each other
+                    if no_inline:
+                        assert np.array_equal(r["rgba"], near["rgba"]) and r["counters"].rays == near["counters"].rays
+                    near = r
+                    continue
+                if ref is None:
+                    ref = r
+                    continue
+                if not no_inline and not host_driven:
+                    fallbacks += r["counters"].fallback_rays
+                    took = r["counters"].traverse_launches * 2 == ref["counters"].traverse_launches or ref["counters"].rays == r["counters"].samples
+                    assert took or b"inline-sun" not in api.load_library().rt_version(), "inline passes were not taken (%d vs %d traverse launches)" % (r["counters"].traverse_launches, ref["counters"].traverse_launches)
+                assert np.array_equal(r["rgba"], ref["rgba"]), "image differs (aa %d, no_inline %s, host %s): %d bytes" % (aa, no_inline, host_driven, (r["rgba"] != ref["rgba"]).sum())
+                assert np.array_equal(r["ids"], ref["ids"]) and np.array_equal(r["written"], ref["written"])
+                assert r["counters"].rays == ref["counters"].rays and r["counters"].samples == ref["counters"].samples
+                assert r["counters"].shaded_hits == ref["counters"].shaded_hits
+    assert fallbacks > 0 or b"inline-sun" not in api.load_library().rt_version(), "no ray went through the reference-order pass in inline mode: the sliver scene should produce some"
+    # planes only (n == 0): the shadow ray is decided without a traversal
+    o = O.OracleScene()
+    o.set_config(width=40, height=30, eye=np.array([0, 1, 0], np.float32))
+    o.add_plane([0, 1, 0, 0], np.array([0.8, 0.7, 0.6, 0, 0, 0, 0, 0, 0, 1.458, 0], np.float32))
+    o.add_plane([1, 0.2, 0, 3], np.array([0.3, 0.7, 0.6, 0, 0, 0, 0, 0, 0, 1.458, 0], np.float32))
+    o.add_sun([0.2, 1, 0.3])
+    monkeypatch.delenv("RT_POOL_BYTES", raising=False); monkeypatch.delenv("RT_HOST_DRIVEN", raising=False)
+    outs = []
+    for no_inline in (False, True):
+        if no_inline: monkeypatch.setenv("RT_NO_INLINE_SUN", "1")
+        else: monkeypatch.delenv("RT_NO_INLINE_SUN", raising=False)
+        sc = H.gpu_scene_from_oracle(o, O.BOUNDS_COMPUTED)
+        outs.append(sc.render(40, 30, 0, want_ids=True)); sc.close()
+    assert np.array_equal(outs[0]["rgba"], outs[1]["rgba"]) and np.array_equal(outs[0]["ids"], outs[1]["ids"]) and outs[0]["counters"].rays == outs[1]["counters"].rays
+    r = o.render(40, 30, 0)
+    assert np.array_equal(outs[0]["ids"], r["ids"]) and np.abs(outs[0]["rgba"].astype(int) - r["rgba"].astype(int)).max() <= 1
