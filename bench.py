@@ -29,6 +29,11 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "Mrays/s @4K, 1M tris + LBVH build ms"
+# the reference keeps the vertex index of a `tri` line in a float (src/parse.cpp:175-180): past 2^24 vertices it reads wrong or
+# out-of-range vertices, so its program cannot load a soup of more than 5 592 405 triangles
+REF_MAX_VERTICES = 1 << 24
+REF_VERTEX_LIMIT_NOTE = ("the reference cannot load this scene: its float-typed vertex index (src/parse.cpp:175-180) is exact only below 2^24 vertices "
+                         "(5 592 405 soup triangles); the reference ratio for a large scene is taken at 5.5M triangles, profiles/vs_gpu_reference_5p5m_r02.json")
 
 
 def parse_args():
@@ -143,7 +148,9 @@ def run_reference(a):
         have_gpu = torch.cuda.is_available()
     except Exception:
         have_gpu = False
-    if have_gpu and os.path.exists(exe):
+    if have_gpu and os.path.exists(exe) and 3 * a.tris >= REF_MAX_VERTICES:
+        gpu = {"unavailable": REF_VERTEX_LIMIT_NOTE}
+    elif have_gpu and os.path.exists(exe):
         from cuda_ray_tracer_b200 import api
         nor, e1, e2 = O.triangle_setup(p0, p1, p2)
         arr = dict(host_arrays); arr["tri"] = [p0, p1, p2, nor, e1, e2]
@@ -230,6 +237,8 @@ def gpu_baseline(a, sc, cfg, arrays, api, synth):
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_fast")
     if not os.path.exists(exe):
         return {"unavailable": "oracle/_ref/ref_gpu_fast was not built (needs /root/reference at build time)"}
+    if 3 * a.tris >= REF_MAX_VERTICES:
+        return {"unavailable": REF_VERTEX_LIMIT_NOTE}
     import oracle_lib as O
     p0, p1, p2 = frame_vertices(arrays, 0)
     nor, e1, e2 = O.triangle_setup(p0, p1, p2)
