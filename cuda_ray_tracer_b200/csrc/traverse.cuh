@@ -562,10 +562,11 @@ __global__ void __launch_bounds__(RT_TRAV_THREADS, WIDE ? RT_WIDE_MIN_CTAS : RT_
           const unsigned avail = chunk_end - chunk_next, want = (unsigned)__popc(idle_m);
           const unsigned take = min(avail, want), rank = (unsigned)__popc(idle_m & ((1u << lane) - 1u));
           bool fetch = st == IDLE && rank < take;
-          float4 q1 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (fetch) { r = chunk_next + rank; q1 = __ldcs(rays + 2 * (size_t)r + 1); fetch = __float_as_uint(q1.w) != RT_RAY_DEAD; }  // DEAD: no ray in this slot
+          float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+          // both halves of the record in one go (ncu: testing the tag before loading q0 put two memory latencies in a row
+          // into every refill, 2 % of the kernel's stall samples); a DEAD slot — no ray — is rare
+          if (fetch) { r = chunk_next + rank; q0 = __ldcs(rays + 2 * (size_t)r); q1 = __ldcs(rays + 2 * (size_t)r + 1); fetch = __float_as_uint(q1.w) != RT_RAY_DEAD; }
           if (fetch) {
-            const float4 q0 = __ldcs(rays + 2 * (size_t)r);
             const V3 o = mk3(q0.x, q0.y, q0.z); d = mk3(q1.x, q1.y, q1.z); tlimit = q0.w;
             const bool anyhit = SUN || (__float_as_uint(q1.w) & RT_RAY_ANYHIT) != 0u;
             const V3 inv = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);  // bvh_traversal.cu:106
