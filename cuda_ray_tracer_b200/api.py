@@ -51,7 +51,7 @@ class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("samples", C.c_uint64), ("nodes_visited", C.c_uint64), ("leaf_tests", C.c_uint64),
                 ("shaded_hits", C.c_uint64), ("wavefront_iters", C.c_uint32), ("passes", C.c_uint32), ("render_ms", C.c_float),
                 ("kernel_launches", C.c_uint32), ("traverse_ms", C.c_float), ("traverse_launches", C.c_uint32),
-                ("fallback_rays", C.c_uint64), ("packet_steps", C.c_uint64)]
+                ("fallback_rays", C.c_uint64), ("d2h_ms", C.c_float), ("reserved0", C.c_uint32), ("packet_steps", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

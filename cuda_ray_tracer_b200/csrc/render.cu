@@ -18,6 +18,7 @@
 // Colours are accumulated with the path weight pushed down ("throughput") instead of being returned up
 // the recursion; the products are the reference's, associated differently (image tolerance 1/255).
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -1448,7 +1449,9 @@ extern "C" int rt_render_host(rt_scene* s, int w, int h, int aa, unsigned flags,
   const size_t npx = (size_t)w * h;
   rc = rt_render(s, w, h, aa, flags, tiles, rs->d_rgba, h_hit_id ? rs->d_ids : nullptr, h_written ? rs->d_written : nullptr, counters, nullptr);
   if (rc) return rc;
+  const auto t_d2h = std::chrono::steady_clock::now();
   RT_CUDA(cudaMemcpy(h_rgba, rs->d_rgba, npx * 4, cudaMemcpyDeviceToHost));  // main.cu:77
+  if (counters) counters->d2h_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_d2h).count();
   if (h_hit_id) RT_CUDA(cudaMemcpy(h_hit_id, rs->d_ids, npx * 4, cudaMemcpyDeviceToHost));
   if (h_written) RT_CUDA(cudaMemcpy(h_written, rs->d_written, npx, cudaMemcpyDeviceToHost));
   return RT_OK;

@@ -152,6 +152,8 @@ typedef struct rt_counters {
   float    traverse_ms;     /* device time inside traverse kernels (RT_COUNTERS / RT_TIME_TRAVERSE) */
   uint32_t traverse_launches;
   uint64_t fallback_rays;   /* exact lane: rays re-traced in reference order (certificate failed)   */
+  float    d2h_ms;          /* rt_render_host: wall time of the device->host copy of the image (main.cu:73-79) */
+  uint32_t reserved0;
   uint64_t packet_steps;    /* node steps of the packet kernel, one per WARP step (RT_COUNTERS): nodes_visited /
                                (32 * packet_steps) = share of the lanes that wanted the node a warp fetched  */
 } rt_counters;
