@@ -31,6 +31,24 @@
 
 namespace {
 
+// Exact division of a 32-bit unsigned number by a divisor that is the same for a whole launch (Granlund & Montgomery's
+// round-up method: q = (t + ((n - t) >> 1)) >> (L - 1), t = umulhi(m, n), L = ceil(log2 d), m = floor(2^32 (2^L - d) / d) + 1;
+// exact for every n < 2^32 — checked against n / d over random and boundary values for d up to 2^32 - 1).  An integer
+// division by a kernel parameter costs ~20 instructions; generate_kernel did seven per sample, one of them on 64 bits.
+struct FastDiv { uint32_t d, m, sh; };
+static FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f; f.d = d ? d : 1u;
+  uint32_t L = 0; while ((1ull << L) < f.d) L++;
+  f.m = (uint32_t)((((1ull << 32) * ((1ull << L) - f.d)) / f.d) + 1ull);
+  f.sh = L;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(const uint32_t n, const FastDiv& f) {
+  if (f.sh == 0u) return n;  // d == 1 (launch-uniform)
+  const uint32_t t = __umulhi(f.m, n);
+  return (t + ((n - t) >> 1)) >> (f.sh - 1u);
+}
+
 // ---- per-render parameters (by value to every kernel) ------------------------------------------
 struct RenderParams {
   RtCamera cam;
@@ -45,7 +63,14 @@ struct RenderParams {
   int full_shade;   // mirrors, glass or GI present: the continuation stack can hold pending calls (shade_kernel<true>)
   int rng_live;     // something after generate draws random numbers (rough materials, gi): the state is stored
   int num_lights;
+  FastDiv fd_spt, fd_tiles_x, fd_sub, fd_bpr, fd_sub_w, fd_spp, fd_tile_w, fd_tile_h, fd_ranks, fd_sub_h, fd_W;  // divisors of slot_to_pixel / pixel_to_slot (set_fastdivs)
 };
+static void set_fastdivs(RenderParams& P) {
+  P.fd_spt = make_fastdiv((uint32_t)P.slots_per_tile); P.fd_tiles_x = make_fastdiv((uint32_t)P.tiles_x); P.fd_sub = make_fastdiv((uint32_t)(P.sub_w * P.sub_h));
+  P.fd_bpr = make_fastdiv((uint32_t)(P.tile_w / P.sub_w)); P.fd_sub_w = make_fastdiv((uint32_t)P.sub_w); P.fd_spp = make_fastdiv((uint32_t)P.spp);
+  P.fd_tile_w = make_fastdiv((uint32_t)P.tile_w); P.fd_tile_h = make_fastdiv((uint32_t)P.tile_h); P.fd_ranks = make_fastdiv((uint32_t)P.num_ranks);
+  P.fd_sub_h = make_fastdiv((uint32_t)P.sub_h); P.fd_W = make_fastdiv((uint32_t)P.W);
+}
 
 struct RenderBuffers {
   uint4 *rng0, *rng1;     // XORWOW v0..v3 | v4, d, box-muller flag, cached normal
@@ -60,6 +85,7 @@ struct RenderBuffers {
   unsigned long long* stats;  // [0] nodes, [1] leaf tests, [2] shaded hits
   const uint32_t* rng_mats;   // power matrices P^m
   const uint32_t* rng_nib;    // the same matrices as 4-bit lookup tables (RT_RNG_NIB_WORDS each)
+  const uint32_t* rng_byte;   // words 0, 1, 4 of the low-seed product as 8-bit lookup tables (RT_RNG_BYTE_STRIDE each)
   const uint32_t* rng_base;   // base vectors for mode 0/1
 };
 
@@ -81,25 +107,26 @@ __device__ __forceinline__ int hdr_bounce(unsigned h) { return (int)(short)((h >
 #define RT_SUB_H 4
 #endif
 __device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, int slot, int& x, int& y, int& pix) {
-  const int lt = slot / P.slots_per_tile, r = slot - lt * P.slots_per_tile;
+  const int lt = (int)fdiv((uint32_t)slot, P.fd_spt), r = slot - lt * P.slots_per_tile;
   const int t = lt * P.num_ranks + P.rank;
-  const int tx = t % P.tiles_x, ty = t / P.tiles_x;
+  const int ty = (int)fdiv((uint32_t)t, P.fd_tiles_x), tx = t - ty * P.tiles_x;
   // inside a tile, slots run over sub_w x sub_h pixel blocks (8 x 4 = one warp) so that the 32 rays of a warp
   // cover a compact footprint and fetch the same nodes; sub = (tile_w, 1) is plain row-major
-  const int sub = P.sub_w * P.sub_h, blk = r / sub, in = r - blk * sub, bpr = P.tile_w / P.sub_w;
-  const int by = blk / bpr, bx = blk - by * bpr, iy = in / P.sub_w;
+  const int sub = P.sub_w * P.sub_h, blk = (int)fdiv((uint32_t)r, P.fd_sub), in = r - blk * sub, bpr = (int)P.fd_bpr.d;
+  const int by = (int)fdiv((uint32_t)blk, P.fd_bpr), bx = blk - by * bpr, iy = (int)fdiv((uint32_t)in, P.fd_sub_w);
   x = tx * P.tile_w + bx * P.sub_w + (in - iy * P.sub_w);
   y = ty * P.tile_h + by * P.sub_h + iy;
   pix = y * P.W + x;
   return x < P.W && y < P.H && pix < P.covered;
 }
 __device__ __forceinline__ bool pixel_to_slot(const RenderParams& P, int pix, int& slot) {
-  const int x = pix % P.W, y = pix / P.W;
-  const int tx = x / P.tile_w, ty = y / P.tile_h;
+  const int y = (int)fdiv((uint32_t)pix, P.fd_W), x = pix - y * P.W;
+  const int tx = (int)fdiv((uint32_t)x, P.fd_tile_w), ty = (int)fdiv((uint32_t)y, P.fd_tile_h);
   const int t = ty * P.tiles_x + tx;
-  if (t % P.num_ranks != P.rank) return false;
-  const int lx = x - tx * P.tile_w, ly = y - ty * P.tile_h, bx = lx / P.sub_w, by = ly / P.sub_h;
-  slot = (t / P.num_ranks) * P.slots_per_tile + (by * (P.tile_w / P.sub_w) + bx) * (P.sub_w * P.sub_h)
+  const int tq = (int)fdiv((uint32_t)t, P.fd_ranks);
+  if (t - tq * P.num_ranks != P.rank) return false;
+  const int lx = x - tx * P.tile_w, ly = y - ty * P.tile_h, bx = (int)fdiv((uint32_t)lx, P.fd_sub_w), by = (int)fdiv((uint32_t)ly, P.fd_sub_h);
+  slot = tq * P.slots_per_tile + (by * (int)P.fd_bpr.d + bx) * (P.sub_w * P.sub_h)
          + (ly - by * P.sub_h) * P.sub_w + (lx - bx * P.sub_w);
   return true;
 }
@@ -186,6 +213,20 @@ __global__ void rng_nibble_kernel(const uint32_t* __restrict__ mats, int count, 
   }
 }
 
+// 8-bit tables out of the 4-bit ones (rng.cuh: xw_matvec_byte_lowseed), built once per table upload
+__global__ void rng_byte_kernel(const uint32_t* __restrict__ nib, int count, uint32_t* __restrict__ byt) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= count * 12 * 256) return;
+  const int m = g / (12 * 256), e = g - m * (12 * 256), p = e >> 8, v = e & 255;
+  const int word = p >> 2, b = p & 3, i = word == 2 ? 4 : word;   // byte b of state word i (0, 1 or 4)
+  const uint32_t* T = nib + (size_t)m * RT_RNG_NIB_STRIDE;
+  const uint32_t* lo = T + ((i * 8 + 2 * b) * 16 + (v & 15)) * 5;
+  const uint32_t* hi = T + ((i * 8 + 2 * b + 1) * 16 + (v >> 4)) * 5;
+  uint32_t* o = byt + (size_t)m * RT_RNG_BYTE_STRIDE + (size_t)e * 3;
+  o[0] = lo[0] ^ hi[0]; o[1] = lo[1] ^ hi[1]; o[2] = lo[4] ^ hi[4];
+  if (e == 0) { uint32_t* c = byt + (size_t)m * RT_RNG_BYTE_STRIDE + RT_RNG_BYTE_WORDS; c[0] = T[RT_RNG_NIB_WORDS]; c[1] = T[RT_RNG_NIB_WORDS + 1]; c[2] = T[RT_RNG_NIB_WORDS + 4]; c[3] = 0u; }
+}
+
 // ---- RNG seeding -------------------------------------------------------------------------------
 // mode 0/1: curand_init(1234, pixel, 0) (draw.cu:105).  Thread g handles pixel h*256 + m with m uniform
 // across the warp, so the 160 matrix rows are broadcast loads (rng.cuh).
@@ -210,16 +251,19 @@ __global__ void __launch_bounds__(256) rng_init_pixels_kernel(const RenderParams
 }
 
 // ---- generate: RNG state, pixel jitter, primary ray (Ray::Ray(x,y,state,cfg), src/struct.cu:16-62) ---
-#define RT_GEN_CHUNKS 4   // a block generates 4 x 256 consecutive samples: the 12.8 KB skip-ahead table is staged once
+#define RT_GEN_CHUNKS 8   // a block generates 8 x 256 consecutive samples: the skip-ahead table (36 KB as 8-bit, 12.8 KB as 4-bit lookups) is staged once
 __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, const RenderBuffers B, float4* __restrict__ qout, int32_t* __restrict__ hit_id_out) {
-  __shared__ uint32_t s_nib[RT_RNG_NIB_STRIDE];
+  // one skip-ahead table per block: the 8-bit one (36 KB) when only the jitter draws read the state, else the 4-bit one (12.8 KB)
+  __shared__ __align__(16) uint32_t s_nib[RT_RNG_BYTE_STRIDE > RT_RNG_NIB_STRIDE ? RT_RNG_BYTE_STRIDE : RT_RNG_NIB_STRIDE];
+  const bool all_words = P.rng_live || P.cam.dof_focus != 0.0f;
   const long long base = (long long)blockIdx.x * (256 * RT_GEN_CHUNKS);
   // sample-major order (i = sample * npix + pixel slot): a block almost always lies inside one sample index,
   // whose skip-ahead matrix all its threads share
-  const int s0 = (int)(base / P.npix);
+  const int s0 = (int)(base / P.npix);  // one 64-bit division per BLOCK (uniform), none per sample
   if (P.mode == 2 && s0 > 0) {
-    const uint4* src = reinterpret_cast<const uint4*>(B.rng_nib + (size_t)s0 * RT_RNG_NIB_STRIDE);
-    for (int k = threadIdx.x; k < RT_RNG_NIB_STRIDE / 4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
+    const uint4* src = reinterpret_cast<const uint4*>(all_words ? B.rng_nib + (size_t)s0 * RT_RNG_NIB_STRIDE : B.rng_byte + (size_t)s0 * RT_RNG_BYTE_STRIDE);
+    const int n4 = (all_words ? RT_RNG_NIB_STRIDE : RT_RNG_BYTE_STRIDE) / 4;
+    for (int k = threadIdx.x; k < n4; k += 256) reinterpret_cast<uint4*>(s_nib)[k] = __ldg(src + k);
     __syncthreads();
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) B.counters[1] = P.cam.bounces != 0 ? (unsigned)P.S : 0u;  // primary rays sit at their sample's slot
@@ -230,7 +274,9 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
   bool live = in_range;
   int s = 0, lp = 0, x = 0, y = 0, pix = 0;
   if (live) {
-    s = (int)(g_ll / P.npix); lp = (int)(g_ll - (long long)s * P.npix);
+    s = s0; long long rem = g_ll - (long long)s0 * P.npix;
+    while (rem >= P.npix) { rem -= P.npix; s++; }  // a block of 1024 samples crosses a sample-index boundary at most a few times (npix >= 32)
+    lp = (int)rem;
     live = slot_to_pixel(P, P.slot0 + lp, x, y, pix);
   }
   // SAMPLE ID (state index, queue slot of the primary ray, ray tag): pixel-major, i = pixel slot * spp + sample, so
@@ -254,8 +300,8 @@ __global__ void __launch_bounds__(256) generate_kernel(const RenderParams P, con
       xw_seed(1234ull + (unsigned long long)pix, v, d);
       if (s == 0) { for (int k = 0; k < 5; k++) out[k] = v[k]; }
       else if (s == s0) {  // 1234 + pix < 2^32
-        if (P.rng_live || P.cam.dof_focus != 0.0f) xw_matvec_nib_lowseed<true>(s_nib, v, out);
-        else xw_matvec_nib_lowseed<false>(s_nib, v, out);  // only the two jitter draws will ever read this state
+        if (all_words) xw_matvec_nib_lowseed<true>(s_nib, v, out);
+        else xw_matvec_byte_lowseed(s_nib, v, out);  // only the two jitter draws will ever read this state: words 0, 1, 4
       }
       else xw_matvec(B.rng_mats + (size_t)s * RT_RNG_MATRIX_WORDS, v, out);  // block straddling two sample indices
       rng.v0 = out[0]; rng.v1 = out[1]; rng.v2 = out[2]; rng.v3 = out[3]; rng.v4 = out[4]; rng.d = d;
@@ -470,7 +516,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_kernel(const Ren
       // T_W_PRIMARY / T_W_GI / T_W_REFLECT / T_W_REFRACT2: the "if hit" body
       const unsigned flag = hdr >> 24;
       if (type == T_W_PRIMARY && hit_id_out) {
-        const int lp = i / P.spp;  // sample ids are pixel-major (generate_kernel)
+        const int lp = (int)fdiv((uint32_t)i, P.fd_spp);  // sample ids are pixel-major (generate_kernel)
         if (i - lp * P.spp == 0) {
           int x, y, pix; slot_to_pixel(P, P.slot0 + lp, x, y, pix);
           int out_id = hid;
@@ -666,7 +712,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_CTAS) shade_inline_kernel(co
       const int i = (int)__float_as_uint(q1.w);
       const float ht = hv.x; const int hid = __float_as_int(hv.y);
       if (hit_id_out) {
-        const int lp = i / P.spp;
+        const int lp = (int)fdiv((uint32_t)i, P.fd_spp);
         if (i - lp * P.spp == 0) {
           int x, y, pix; slot_to_pixel(P, P.slot0 + lp, x, y, pix);
           int out_id = hid;
@@ -795,6 +841,7 @@ __global__ void unpack_hits_kernel(const float2* __restrict__ hits, const uint32
 struct RngTables {  // device copies of the skip-ahead matrices, one set per device
   uint32_t* mats = nullptr; int mats_count = 0;
   uint32_t* nib = nullptr;
+  uint32_t* byt = nullptr;
   uint32_t* base = nullptr; int base_count = 0;
 };
 
@@ -982,6 +1029,9 @@ int ensure_rng_tables(RenderState* st, int mats_needed, int base_needed) {
     if (st->rng.nib) cudaFree(st->rng.nib);
     RT_CUDA(cudaMalloc(&st->rng.nib, (size_t)mats_needed * RT_RNG_NIB_STRIDE * 4));
     rng_nibble_kernel<<<(mats_needed * 640 + 255) / 256, 256>>>(st->rng.mats, mats_needed, st->rng.nib);
+    if (st->rng.byt) cudaFree(st->rng.byt);
+    RT_CUDA(cudaMalloc(&st->rng.byt, (size_t)mats_needed * RT_RNG_BYTE_STRIDE * 4));
+    rng_byte_kernel<<<(mats_needed * 12 * 256 + 255) / 256, 256>>>(st->rng.nib, mats_needed, st->rng.byt);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaDeviceSynchronize());
     st->rng.mats_count = mats_needed;
@@ -1009,7 +1059,7 @@ int rt_render_free_state(rt_scene* s) {
   RenderState* st = (RenderState*)s->rstate;
   if (!st) return RT_OK;
   cudaFree(st->pool[0]); cudaFree(st->pool[1]); cudaFree(st->counters); cudaFree(st->stats); cudaFreeHost(st->h_count);
-  cudaFree(st->rng.mats); cudaFree(st->rng.nib); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
+  cudaFree(st->rng.mats); cudaFree(st->rng.nib); cudaFree(st->rng.byt); cudaFree(st->rng.base); cudaFree(st->d_rgba); cudaFree(st->d_ids); cudaFree(st->d_written);
   cudaFree(st->trace_q); cudaFree(st->trace_hits); cudaFree(st->trace_fb);
   if (st->e0) {
     cudaEventDestroy(st->e0); cudaEventDestroy(st->e1);
@@ -1065,6 +1115,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
   else { P.sub_w = P.tile_w; P.sub_h = 1; }
   long long nslots = owned * P.slots_per_tile;
   if (!tiles && P.covered < npx) { P.sub_w = P.tile_w; P.sub_h = 1; nslots = P.covered; }  // F3's partial image, one tile: slot == pixel
+  set_fastdivs(P);  // every divisor of the slot <-> pixel maps is final here
   P.ref_order = lane_of(flags);
   P.rough_zyx = (flags & RT_ROUGH_ZYX) ? 1 : 0;
   const bool count = (flags & RT_COUNTERS) != 0;
@@ -1163,7 +1214,7 @@ extern "C" int rt_render(rt_scene* s, int w, int h, int aa, unsigned flags, cons
     B.hits = (float2*)p; p += al(Smax * 8);
     B.fb_list = (unsigned*)p; p += al(Smax * 4);
     c.counters = rs->counters + 256 * k; c.h_count = rs->h_count + 16 * k;  // 16 counter blocks of 16 words per context
-    B.counters = c.counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_base = rs->rng.base;
+    B.counters = c.counters; B.stats = rs->stats; B.rng_mats = rs->rng.mats; B.rng_nib = rs->rng.nib; B.rng_byte = rs->rng.byt; B.rng_base = rs->rng.base;
     c.st = k == 0 ? st : rs->pass_stream;
     c.ev_cnt = rs->ev_cnt[k]; c.t0 = rs->t0[k]; c.t1 = rs->t1[k];
   }

@@ -95,6 +95,26 @@ __device__ __forceinline__ void xw_matvec_nib_lowseed(const uint32_t* tab, const
   out[0] = r0; out[1] = r1; out[2] = r2; out[3] = r3; out[4] = r4;
 }
 
+// 8-bit tables for the same low-seed product when only words 0, 1 and 4 of the result are wanted (the pixel jitter's two
+// draws): T8[p][v] = T4[2p][v & 15] ^ T4[2p + 1][v >> 4] for the 12 byte positions of v0, v1, v4, three words per entry:
+// 12 x 256 x 3 words = 36 KB per matrix, 12 lookups x (3 loads + 3 xors) instead of 24 x.  Entry stride 3 words (odd), so
+// 32 lanes with different byte values spread over the banks.  [RT_RNG_BYTE_WORDS .. +3) = the seed-independent share.
+#define RT_RNG_BYTE_WORDS (12 * 256 * 3)
+#define RT_RNG_BYTE_STRIDE (RT_RNG_BYTE_WORDS + 4)
+__device__ __forceinline__ void xw_matvec_byte_lowseed(const uint32_t* tab, const uint32_t* in, uint32_t* out) {
+  uint32_t r0 = tab[RT_RNG_BYTE_WORDS], r1 = tab[RT_RNG_BYTE_WORDS + 1], r4 = tab[RT_RNG_BYTE_WORDS + 2];
+#pragma unroll
+  for (int ii = 0; ii < 3; ii++) {
+    const uint32_t w = in[ii == 2 ? 4 : ii];
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+      const uint32_t* e = tab + ((ii * 4 + b) * 256 + ((w >> (8 * b)) & 255u)) * 3;
+      r0 ^= e[0]; r1 ^= e[1]; r4 ^= e[2];
+    }
+  }
+  out[0] = r0; out[1] = r1; out[2] = 0u; out[3] = 0u; out[4] = r4;
+}
+
 // The same product through 4-bit tables (method of the four Russians): T[p][v] = XOR of the rows 4p+b, b in v,
 // 40 nibble positions x 16 values x 5 words = 12.8 KB per matrix, staged in shared memory by the caller.  An
 // entry is 5 words, so the 16 entries of a position start in 16 different banks: lanes with different nibble
