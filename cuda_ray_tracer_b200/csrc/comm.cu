@@ -190,23 +190,23 @@ extern "C" int rt_comm_num_local(const rt_comm* c) { return c ? (int)c->dev.size
 extern "C" int rt_comm_local_rank(const rt_comm* c, int local) { return (c && local >= 0 && local < (int)c->rank.size()) ? c->rank[local] : -1; }
 extern "C" int rt_comm_local_device(const rt_comm* c, int local) { return (c && local >= 0 && local < (int)c->dev.size()) ? c->dev[local] : -1; }
 
-// 256-pixel tile shape for `ranks` GPUs.  Tile t (row-major) belongs to rank t % ranks, so when the number of tiles per
-// image row is a multiple of `ranks` every rank would own whole COLUMNS of tiles and the load would follow the
-// picture's horizontal structure (measured: 7 % spread at 8 GPUs on the 4K soup).  Picks the shape whose tiles-per-row
-// shares the fewest factors with `ranks` (ties: least padding, then the squarest): 256x1 at 3840 wide = 15 tiles per
-// row, a diagonal ownership pattern.
+// Tile shape for `ranks` GPUs.  Tile t (row-major) belongs to rank t % ranks, so when the number of tiles per image row is
+// a multiple of `ranks` every rank would own whole COLUMNS of tiles and the load would follow the picture's horizontal
+// structure.  Candidates are 8 rows high (two rows of the 8 x 4 pixel blocks a warp's slots run over; 1-row tiles fall
+// back to row-major slots and measured ~2 % slower for the slowest rank: profiles/tile_shape_scan_r02.txt) and 32..1280
+// wide; the choice minimises, in this order, the common factor of tiles-per-row and `ranks`, the padding of the last tile
+// in a row, and the tile size (finer interleave = better balance): 256 x 8 at 3840 wide (15 tiles per row, diagonal
+// ownership), 128 x 8 at 1920.
 extern "C" void rt_tile_shape(int ranks, int width, int* tile_w, int* tile_h) {
-  static const int shapes[5][2] = {{32, 8}, {64, 4}, {16, 16}, {128, 2}, {256, 1}};
+  static const int widths[] = {32, 64, 96, 128, 160, 256, 384, 512, 640, 768, 1280};
   int bw = 32, bh = 8;
   if (ranks > 1 && width > 0) {
     long long best[3] = {1ll << 60, 0, 0};
-    for (const auto& sh : shapes) {
-      const int tx = (width + sh[0] - 1) / sh[0];
+    for (const int wdt : widths) {
+      const int tx = (width + wdt - 1) / wdt;
       int a = tx, b = ranks; while (b) { const int t = a % b; a = b; b = t; }  // gcd
-      int lg = 0; for (int q = sh[0] / sh[1]; q > 1; q >>= 1) lg++;
-      for (int q = sh[1] / sh[0]; q > 1; q >>= 1) lg++;
-      const long long key[3] = {a, (long long)tx * sh[0] - width, lg};
-      if (std::lexicographical_compare(key, key + 3, best, best + 3)) { best[0] = key[0]; best[1] = key[1]; best[2] = key[2]; bw = sh[0]; bh = sh[1]; }
+      const long long key[3] = {a, (long long)tx * wdt - width, wdt};
+      if (std::lexicographical_compare(key, key + 3, best, best + 3)) { best[0] = key[0]; best[1] = key[1]; best[2] = key[2]; bw = wdt; }
     }
   }
   if (tile_w) *tile_w = bw;

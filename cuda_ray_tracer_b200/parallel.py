@@ -8,8 +8,8 @@ TILE_W, TILE_H = 32, 8
 
 
 def tile_shape(world, width=None):
-    """256-pixel tile shape for `world` ranks: rt_tile_shape (csrc/comm.cu) — the shape whose tiles-per-row shares the
-    fewest factors with world, so that no rank owns whole columns of tiles (256x1 at 3840 wide: a diagonal pattern)."""
+    """tile shape for `world` ranks: rt_tile_shape (csrc/comm.cu) — 8-row tiles whose count per image row shares the
+    fewest factors with world, so that no rank owns whole columns of tiles (256x8 at 3840 wide: a diagonal pattern)."""
     if width is None or world <= 1:
         return TILE_W, TILE_H
     return api.tile_shape(world, width)

@@ -33,15 +33,17 @@ def test_comm_fails_loudly_without_enough_gpus():
 
 
 def test_tile_shape_c_matches_the_rule():
-    # tiles per row must share as few factors with the rank count as possible
-    assert api.tile_shape(8, 3840) == (256, 1)      # 15 tiles per row
+    # 8-row tiles; tiles per row must share as few factors with the rank count as possible, then least padding, then smallest
+    assert api.tile_shape(8, 3840) == (256, 8)      # 15 tiles per row
+    assert api.tile_shape(8, 1920) == (128, 8)      # 15 tiles per row
     assert api.tile_shape(1, 3840) == (32, 8)
+    widths = (32, 64, 96, 128, 160, 256, 384, 512, 640, 768, 1280)
     for ranks in (2, 3, 4, 8):
-        for width in (640, 1920, 3840, 1000):
+        for width in (640, 1920, 3840, 1000, 100):
             tw, th = api.tile_shape(ranks, width)
-            assert tw * th == 256
+            assert th == 8 and tw in widths
             g = np.gcd((width + tw - 1) // tw, ranks)
-            assert g == min(np.gcd((width + a - 1) // a, ranks) for a in (32, 64, 16, 128, 256))
+            assert g == min(np.gcd((width + a - 1) // a, ranks) for a in widths)
 
 
 def _scene_desc(n=20000, w=160, h=96, aa=4):
