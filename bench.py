@@ -372,6 +372,8 @@ def run_b200(a):
 
     def timed(fn, steps, warmup, smp=None):
         cnt = api.Counters()
+        if world > 1:
+            dist.barrier()  # the first barrier of a leg has one-time costs (observed: a 9.9 ms first timed step at 8 GPUs): pay them before the warm-up
         for f in range(warmup):
             fn(f, cnt); flush.fill_(f & 255)
         torch.cuda.synchronize()
