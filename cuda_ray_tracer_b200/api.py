@@ -16,7 +16,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libb200rt.so")  # RT_LIB: experiment builds (Makefile LIB=...)
 
-BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN, BUILD_LOCAL_CLIMB, BUILD_WIDE4 = 0, 1, 2, 4, 8
+BOUNDS_FROM_DESC, BOUNDS_COMPUTED, BUILD_TOPDOWN, BUILD_LOCAL_CLIMB, BUILD_WIDE4, BUILD_GLOBAL_CLIMB = 0, 1, 2, 4, 8, 16
 SPP_REF, SPP_TRUE, TRAVERSE_NEAR_FIRST, ROUGH_ZYX, COUNTERS, TIME_TRAVERSE, TRAVERSE_REF_ORDER, RENDER_OVERLAP_BUILD, RENDER_SERIAL_PASSES = 0, 1, 2, 4, 8, 16, 32, 64, 128
 TRAVERSE_PACKET = 256
 

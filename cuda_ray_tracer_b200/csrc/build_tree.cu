@@ -18,6 +18,8 @@
 //  * RT_BUILD_TOPDOWN: per-node range and split search exactly as the reference does it, in the
 //    reference's numbering, followed by the atomic bottom-up refit with the fence the reference
 //    lacks.
+#include <cstdlib>
+#include <cstring>
 #include "build.cuh"
 
 namespace {
@@ -70,6 +72,12 @@ __device__ __forceinline__ int exch_acq_rel(int* addr, int v) {
   return old;
 }
 
+__device__ __forceinline__ int ld_acquire(const int* addr) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.b32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+
 // ---- fused bottom-up builder ------------------------------------------------------------------
 template <typename KeyT>
 __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ perm,
@@ -108,6 +116,132 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
     slack = fmaxf(slack, load_half_box(nodes, s, side ^ 1, sib));
     if (side == 0) { r = other; box = union_box(box, sib); } else { l = other; box = union_box(sib, box); }
     ref = (uint32_t)s;
+  }
+}
+
+// ---- fused bottom-up builder, lower levels inside the warp (default since round 2) -----------------------------------
+// ncu on bottom_up_kernel (profiles/ncu_build_r02.txt): 9 of 32 lanes per instruction, 14 % of the issue slots, long_scoreboard
+// 36 per issue: a warp stays resident until its last lane has finished a climb of dependent device-scope exchanges, and
+// most of that time most of its lanes are dead.  Here the 32 consecutive leaves of a warp first meet INSIDE the warp: in
+// every round each live lane (a finished subtree [l, r]) names its parent s and side exactly as above; two live lanes that
+// name the same parent are its two children (__match_any_sync), the left one takes the right one's half by shuffle, writes
+// the finished 64-byte node and goes on with the union, the right one retires.  No flag, no atomic, no global read for a
+// node whose children both lie in the warp (about 26 of 31).  Rounds stop when none pairs up; what is left (subtrees whose
+// sibling reaches beyond the warp's 32 leaves) continues with the global protocol of bottom_up_kernel.  Same tree, same
+// boxes: fminf / fmaxf unions do not depend on who forms them (tests/test_build_gpu.py runs every size with both kernels).
+// Measured (profiles/build_climb_r02.txt) against the round-1 kernel, with the survivor compaction and the look before the
+// exchange below: 1M 0.295 vs 0.302 ms, 10M 2.117 vs 2.304 ms (-8 %).  The split the leaf-only run gives at 1M: codes + sort
+// 0.136, leaf records 0.054, climb 0.105 ms - of which ~0.04 is the chain to the root (the whole climb of a 100K build,
+// one wave of blocks, 17 levels, takes 0.037 ms) - so what happens to the lower levels moves little.
+// mode bit 0: TIMING EXPERIMENT ONLY (scripts/build_ab.py, RT_BU_LEAFONLY): stop after the leaf records, no tree.
+template <typename KeyT>
+__global__ void __launch_bounds__(256) bottom_up_warp_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ perm,
+                                                            const float4* __restrict__ bv, const float4* __restrict__ tv,
+                                                            float4* __restrict__ sorted_tv, float4* nodes, int* flags, int n,
+                                                            int* root_out, float* root_box, const int mode) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31;
+  const int k0 = k - (int)lane, klast = min(k0 + 31, n - 1);  // the warp's leaves
+  bool active = k < n;
+  RtBox box; box.xmin = box.ymin = box.zmin = box.xmax = box.ymax = box.zmax = 0.f;
+  float slack = 0.f; uint32_t ref = 0u;
+  if (active) {
+    const uint32_t p = perm[k];
+    const float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)p), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)p + 2);
+    const float4 t0 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p), t1 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 1), t2 = __ldg(tv + RT_PRIM_STRIDE * (size_t)p + 2);
+    box = rt_prim_box(a, b, c);
+    float4* rec = sorted_tv + RT_TV_STRIDE * (size_t)k;
+    rec[0] = t0; rec[1] = t1; rec[2] = t2; rec[3] = make_float4(__uint_as_float(p), 0.f, 0.f, 0.f);
+    rec[4] = make_float4(box.xmin, box.ymin, box.xmax, box.ymax); rec[5] = make_float4(box.zmin, box.zmax, 0.f, 0.f);
+    slack = c.y;
+    ref = RT_LEAF_BIT | (c.w == RT_TAG_SPHERE ? RT_SPHERE_BIT : 0u) | (uint32_t)k;
+  }
+  if (mode & 1) return;
+  Delta<KeyT> D{keys, n};
+  int l = k, r = k, s = -1, side = 0, dl = -1, dr = -1;
+  bool need = true;  // (s, side) must be (re)computed: the range has changed
+  while (true) {     // ---- rounds inside the warp ----
+    if (active && need) {
+      if (l == 0 && r == n - 1) {  // root (n <= 32, or the first warp of a tiny tree)
+        *root_out = (int)ref;
+        root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+        active = false;
+      } else {
+        dl = D.adj(l - 1); dr = D.adj(r);
+        if (dr > dl) { s = r; side = 0; } else { s = l - 1; side = 1; }
+        need = false;
+      }
+    }
+    // the sibling can lie inside the warp only if it starts (side 0: at s + 1) or ends (side 1: at s) there
+    const bool cand = active && (side == 0 ? s + 1 <= klast : s >= k0);
+    const unsigned peers = __match_any_sync(0xffffffffu, cand ? (unsigned)s : (0x80000000u | lane));
+    const bool pair = cand && __popc(peers) == 2;
+    if (!__any_sync(0xffffffffu, pair)) break;
+    const int partner = pair ? (__ffs(peers & ~(1u << lane)) - 1) : (int)lane;
+    RtBox pb;
+    pb.xmin = __shfl_sync(0xffffffffu, box.xmin, partner); pb.ymin = __shfl_sync(0xffffffffu, box.ymin, partner); pb.zmin = __shfl_sync(0xffffffffu, box.zmin, partner);
+    pb.xmax = __shfl_sync(0xffffffffu, box.xmax, partner); pb.ymax = __shfl_sync(0xffffffffu, box.ymax, partner); pb.zmax = __shfl_sync(0xffffffffu, box.zmax, partner);
+    const float pslack = __shfl_sync(0xffffffffu, slack, partner);
+    const uint32_t pref = __shfl_sync(0xffffffffu, ref, partner);
+    const int pr = __shfl_sync(0xffffffffu, r, partner);
+    if (pair) {
+      if (side == 0) {  // the left child writes the finished node and goes on
+        store_half(nodes, s, 0, box, ref, slack);
+        store_half(nodes, s, 1, pb, pref, pslack);
+        box = union_box(box, pb); slack = fmaxf(slack, pslack); r = pr; ref = (uint32_t)s; need = true;
+      } else active = false;  // the right child has handed its half over
+    }
+  }
+  // here every live lane knows dl = delta(l-1, l), dr = delta(r, r+1) of its subtree, and none is the root
+  if (mode & 2) {  // the block's survivors (about 9 per warp) move into its first warps, the other warps leave the SM
+    __shared__ int s_cnt;
+    __shared__ float s_state[12][256];
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    const unsigned m = __ballot_sync(0xffffffffu, active);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(&s_cnt, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (active) {
+      const int q = base + __popc(m & ((1u << lane) - 1u));
+      s_state[0][q] = box.xmin; s_state[1][q] = box.ymin; s_state[2][q] = box.zmin; s_state[3][q] = box.xmax; s_state[4][q] = box.ymax; s_state[5][q] = box.zmax;
+      s_state[6][q] = slack; s_state[7][q] = __uint_as_float(ref); s_state[8][q] = __int_as_float(l); s_state[9][q] = __int_as_float(r);
+      s_state[10][q] = __int_as_float(dl); s_state[11][q] = __int_as_float(dr);
+    }
+    __syncthreads();
+    const int q = threadIdx.x;
+    active = q < s_cnt;
+    if (active) {
+      box.xmin = s_state[0][q]; box.ymin = s_state[1][q]; box.zmin = s_state[2][q]; box.xmax = s_state[3][q]; box.ymax = s_state[4][q]; box.zmax = s_state[5][q];
+      slack = s_state[6][q]; ref = __float_as_uint(s_state[7][q]); l = __float_as_int(s_state[8][q]); r = __float_as_int(s_state[9][q]);
+      dl = __float_as_int(s_state[10][q]); dr = __float_as_int(s_state[11][q]);
+    }
+  }
+  if (!active) return;
+  while (true) {  // ---- what is left: the global protocol of bottom_up_kernel, one dependent round trip shorter per level ----
+    int mine;
+    if (dr > dl) { s = r; side = 0; mine = l; } else { s = l - 1; side = 1; mine = r; }
+    store_half(nodes, s, side, box, ref, slack);
+    int other = -1;
+    // look before the exchange: a child that finds its sibling's mark needs no release of its own half (nobody reads it
+    // through this flag) and skips MEMBAR.ALL.GPU + the atomic's round trip; the chain that ends at the root is the late
+    // child of every level.  -3 % at 1M, -2 % at 10M (profiles/build_climb_r02.txt)
+    if (mode & 4) other = ld_acquire(flags + s);
+    if (other == -1) other = exch_acq_rel(flags + s, mine);
+    if (other == -1) return;
+    // both loads that depend on the exchange go out together: the sibling's half and the two keys at the new far edge
+    // (the near edge's delta is unchanged)
+    RtBox sib;
+    const float sslack = load_half_box(nodes, s, side ^ 1, sib);
+    const int dnew = side == 0 ? D.adj(other) : D.adj(other - 1);
+    slack = fmaxf(slack, sslack);
+    if (side == 0) { r = other; dr = dnew; box = union_box(box, sib); } else { l = other; dl = dnew; box = union_box(sib, box); }
+    ref = (uint32_t)s;
+    if (l == 0 && r == n - 1) {
+      *root_out = (int)ref;
+      root_box[0] = box.xmin; root_box[1] = box.xmax; root_box[2] = box.ymin; root_box[3] = box.ymax; root_box[4] = box.zmin; root_box[5] = box.zmax;
+      return;
+    }
   }
 }
 
@@ -441,6 +575,9 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
   rc = rt_build_codes_and_sort(s, morton_bits, flags, st, &launches);
   if (rc) return rc;
   const int n = s->n, grid = (n + 255) / 256;
+    // RT_BU_LEAFONLY=1: timing experiment of scripts/build_ab.py (leaf records only, NO tree) - never set it otherwise
+  const int bu_mode = (flags & RT_BUILD_GLOBAL_CLIMB) ? 0 : 1;
+  const int bu_bits = (getenv("RT_BU_LEAFONLY") ? 1 : 0) | (getenv("RT_BU_NO_COMPACT") ? 0 : 2) | (getenv("RT_BU_NO_PEEK") ? 0 : 4);  // env switches: scripts/build_ab.py only
   int* root_dev = (int*)(s->bounds + 8);
   float* root_box = s->bounds + 10;
   if (flags & RT_BUILD_TOPDOWN) {
@@ -451,9 +588,11 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
     refit_kernel<<<grid, 256, 0, st>>>(s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->parent, s->node_flags, n, root_dev, root_box);
   } else if (!(flags & RT_BUILD_LOCAL_CLIMB)) {
     if (morton_bits == 30)
-      bottom_up_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+      if (bu_mode == 0) bottom_up_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+      else bottom_up_warp_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits);
     else
-      bottom_up_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+      if (bu_mode == 0) bottom_up_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
+      else bottom_up_warp_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits);
   } else {
     const int gl = (n + RT_BU_CHUNK - 1) / RT_BU_CHUNK;
     if (morton_bits == 30)

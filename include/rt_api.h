@@ -77,8 +77,11 @@ enum {
   RT_BUILD_TOPDOWN      = 2u,  /* per-node Karras range/split search (lbvh_builder.cu:103-322) +
                                   separate refit instead of the fused bottom-up builder           */
   RT_BUILD_LOCAL_CLIMB  = 4u,  /* fused bottom-up builder whose levels inside a 512-leaf chunk meet in shared
-                                  memory (default: every level through global atomics); same tree,
+                                  memory (then the global flags); same tree,
                                   measured no faster (the primitive gather bounds the kernel), kept for A/B */
+  RT_BUILD_GLOBAL_CLIMB = 16u, /* fused bottom-up builder with EVERY level through the global flags (round 1's kernel).  The
+                                  default since round 2 lets the 32 leaves of a warp meet by shuffle first; same tree.
+                                  Kept for A/B (scripts/build_ab.py) and so the tests hold both against the oracle */
   RT_BUILD_WIDE4        = 8u   /* EXPERIMENTAL: after the LBVH, derive a 4-wide tree over the same leaves (a node's
                                   children = its grandchildren, 128-byte nodes).  The near-first lanes of rt_render /
                                   rt_trace then step through it (half the dependent steps per ray); the exported

@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from cuda_ray_tracer_b200 import api, synth
 label = sys.argv[1] if len(sys.argv) > 1 else os.path.basename(api.LIB_PATH)
-for n in (1_000_000, 10_000_000):
+for n in (100_000, 1_000_000, 10_000_000):
     cfg, a = synth.soup(n, 1, 64, 64, 0)
     p0, p1, p2 = a["tri"][:3]
     nor, e1, e2 = api.triangle_setup(p0, p1, p2)
@@ -14,15 +14,21 @@ for n in (1_000_000, 10_000_000):
     desc, keep = api.make_desc(cfg, a)
     sc = api.Scene(desc, 0)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    for bits in (30, 63):
-        ms = []
-        for k in range(12):
-            sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2]); flush.fill_(k); torch.cuda.synchronize()
-            ms.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED))
-        warm = []
-        for k in range(6):  # the frame loop's case: the vertex update has just written the records
-            sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2])
-            warm.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED))
-        print("%-10s n=%8d bits=%d  build after L2 flush: best %.3f median %.3f ms | right after update_triangles: best %.3f ms" % (
-            label, n, bits, min(ms), statistics.median(ms), min(warm)))
+    # climb variants of the fused builder: warp-first (default), every level global (round 1), and - timing only, no tree -
+    # the leaf phase alone (RT_BU_LEAFONLY), which splits the kernel into gather/records and climb
+    for mode, fl, env in (("default", 0, None), ("no peek", 0, "RT_BU_NO_PEEK"), ("no compact", 0, "RT_BU_NO_COMPACT"), ("global", api.BUILD_GLOBAL_CLIMB, None), ("leaf-only", 0, "RT_BU_LEAFONLY")):
+        for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK"): os.environ.pop(e, None)
+        if env: os.environ[env] = "1"
+        for bits in (30, 63):
+            ms = []
+            for k in range(12):
+                sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2]); flush.fill_(k); torch.cuda.synchronize()
+                ms.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED | fl))
+            warm = []
+            for k in range(6):  # the frame loop's case: the vertex update has just written the records
+                sc.update_triangles(a["tri"][0], a["tri"][1], a["tri"][2])
+                warm.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED | fl))
+            print("%-6s %-12s n=%8d bits=%d  build after L2 flush: best %.3f median %.3f ms | right after update_triangles: best %.3f ms" % (
+                label, mode, n, bits, min(ms), statistics.median(ms), min(warm)))
+    for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK"): os.environ.pop(e, None)
     sc.close(); del sc, a

@@ -30,7 +30,7 @@ def check_build(o, mode, bits, flags_extra=0):
 
 @pytest.mark.parametrize("name", H.SCENES)
 @pytest.mark.parametrize("mode", [O.BOUNDS_SHIPPED, O.BOUNDS_COMPUTED])
-@pytest.mark.parametrize("topdown", [0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB])
+@pytest.mark.parametrize("topdown", [0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB, api.BUILD_GLOBAL_CLIMB])
 def test_build_scene_files(name, mode, topdown):
     p = H.scene_path(name)
     if p is None:
@@ -62,7 +62,7 @@ def test_build_soup_sizes(n, bits):
         e = sc.export_reference_layout(bits)
         assert e["nleaf"][0] == 1 and e["perm"][0] == 0
         return
-    for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB):
+    for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB, api.BUILD_GLOBAL_CLIMB):
         check_build(o, O.BOUNDS_COMPUTED, bits, td)
     check_build(o, O.BOUNDS_SHIPPED, bits)
 
@@ -71,7 +71,7 @@ def test_build_mixed_duplicates():
     cfg, a = H.mixed_scene(5000)
     o = H.oracle_from_arrays(cfg, a)
     for bits in (30, 63):
-        for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB):
+        for td in (0, api.BUILD_TOPDOWN, api.BUILD_LOCAL_CLIMB, api.BUILD_GLOBAL_CLIMB):
             check_build(o, O.BOUNDS_COMPUTED, bits, td)
 
 
@@ -82,7 +82,9 @@ def test_build_1m_soup_properties_and_parity():
     o = H.oracle_from_arrays(cfg, a)
     ms = check_build(o, O.BOUNDS_COMPUTED, 30)
     ms_l = check_build(o, O.BOUNDS_COMPUTED, 30, api.BUILD_LOCAL_CLIMB)
-    print("1M build ms: global climb %.3f, block-local climb %.3f" % (ms, ms_l))
+    ms_g = check_build(o, O.BOUNDS_COMPUTED, 30, api.BUILD_GLOBAL_CLIMB)
+    check_build(o, O.BOUNDS_COMPUTED, 63); check_build(o, O.BOUNDS_SHIPPED, 30)  # all codes equal: the deepest chains
+    print("1M build ms: warp-first climb %.3f, global climb %.3f, block-local climb %.3f" % (ms, ms_g, ms_l))
 
 
 def test_sort_is_stable_permutation_vs_torch():
