@@ -1,6 +1,7 @@
 // build.cuh — internal interface between build_sort.cu (bounds, Morton codes, onesweep radix sort)
 // and build_tree.cu (hierarchy, refit, export, rt_build_lbvh).
 #pragma once
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -92,3 +93,29 @@ __device__ inline float rt_leaf_slack(float4 a, float4 b, float4 c, float4 t0, f
 
 // build_sort.cu
 int rt_build_codes_and_sort(rt_scene* s, int morton_bits, unsigned flags, cudaStream_t st, uint32_t* launches);
+
+// ---- programmatic dependent launch along the build's chain of kernels ----------------------------------------------
+// The build is nine short kernels in a row, each waiting for the previous one (init, bounds, Morton, 4-8 sort passes,
+// bottom-up); none fills the GPU for long, so the ~3 us it takes to drain one grid and start the next is paid nine
+// times.  Launched with cudaLaunchAttributeProgrammaticStreamSerialization, a kernel's blocks may become resident while
+// the previous grid's last blocks still run (the previous kernel says so first thing, rt_pdl_trigger); they do whatever
+// does not touch global memory (zeroing shared counters) and then block in rt_pdl_wait until the previous grid has
+// COMPLETED and its writes are visible.  Every kernel of the chain waits unconditionally at its top, so completion is
+// transitive.  Both instructions are no-ops in a kernel launched the ordinary way.  RT_NO_PDL=1: ordinary launches (A/B).
+__device__ __forceinline__ void rt_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void rt_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Measured (profiles/build_pdl_r02.txt): 100K 0.114 -> 0.103 ms, 1M 0.293 -> 0.292 (30-bit) / 0.432 -> 0.413 (63-bit), but 10M
+// 30-bit 2.125 -> 2.278 ms: long passes gain nothing from a 3 us hand-over and lose to the next pass's blocks sitting on the
+// SMs early.  So the chain is used up to 4M primitives.
+#define RT_PDL_MAX_N (1 << 22)
+inline bool rt_pdl_for(int n) { return n <= RT_PDL_MAX_N && getenv("RT_NO_PDL") == nullptr; }  // env read per build: scripts/build_ab.py flips it in-process
+template <typename... Params, typename... Args>
+inline cudaError_t rt_launch_chained(bool dependent, void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = dependent ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, Params(args)...);
+}

@@ -30,6 +30,7 @@ constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_VAL = (1u << 30) - 1
 // ---- state init: one launch instead of four memsets -------------------------------------------
 __global__ void init_build_state_kernel(uint32_t* hist, int hist_words, uint32_t* lookback, size_t lb_words, uint32_t* tickets,
                                         uint32_t* bounds_enc, float3 mn, float3 mx) {
+  rt_pdl_trigger();
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
   for (size_t k = i; k < (size_t)hist_words; k += stride) hist[k] = 0;
   for (size_t k = i; k < lb_words; k += stride) lookback[k] = 0;
@@ -42,6 +43,7 @@ __global__ void init_build_state_kernel(uint32_t* hist, int hist_words, uint32_t
 
 // ---- scene bounds: fminf/fmaxf over the primitive AABBs (parse.cpp:147-155,193-200) -----------
 __global__ void __launch_bounds__(256) bounds_kernel(const float4* __restrict__ bv, int n, uint32_t* bounds_enc) {
+  rt_pdl_trigger(); rt_pdl_wait();
   float mnx = INFINITY, mny = INFINITY, mnz = INFINITY, mxx = -INFINITY, mxy = -INFINITY, mxz = -INFINITY;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     float4 a = __ldg(bv + RT_PRIM_STRIDE * (size_t)i), b = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 1), c = __ldg(bv + RT_PRIM_STRIDE * (size_t)i + 2);
@@ -95,7 +97,9 @@ __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ 
                                                     KeyT* __restrict__ keys, uint32_t* __restrict__ perm, uint32_t* __restrict__ hist,
                                                     int* __restrict__ node_flags) {
   __shared__ uint32_t s_hist[NPASS][256];
+  rt_pdl_trigger();
   for (int k = threadIdx.x; k < NPASS * 256; k += blockDim.x) (&s_hist[0][0])[k] = 0;
+  rt_pdl_wait();  // the bounds (and the zeroed histograms) come from the kernels before
   __syncthreads();
   const float mnx = rt_float_unorder(bounds_enc[0]), mny = rt_float_unorder(bounds_enc[1]), mnz = rt_float_unorder(bounds_enc[2]);
   const float rx = rt_float_unorder(bounds_enc[3]) - mnx, ry = rt_float_unorder(bounds_enc[4]) - mny,
@@ -156,8 +160,10 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  rt_pdl_trigger();
   for (int k = tid; k < SORT_WARPS * 256; k += SORT_THREADS) (&s_warp[0][0])[k] = 0;
+  rt_pdl_wait();  // the previous pass (or the Morton kernel) must be complete before a ticket is taken
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
   // a digit every key shares makes the pass the identity: copy the tile and leave
   const int trivial = __syncthreads_or(hist[tid] == (uint32_t)n);
   const uint32_t tile = s_tile;
@@ -309,11 +315,11 @@ int sort_impl(rt_scene* s, cudaStream_t st, uint32_t* launches) {
   uint32_t *pa = s->perm_a, *pb = s->perm_b;
   int grid = (n + 255) / 256;
   if (grid > 148 * 8) grid = 148 * 8;
-  morton_kernel<KeyT, NPASS><<<grid, 256, 0, st>>>(s->prim_bv, n, (const uint32_t*)s->bounds, ka, pa, s->hist, s->node_flags);
+  RT_CUDA(rt_launch_chained(rt_pdl_for(n), morton_kernel<KeyT, NPASS>, dim3(grid), dim3(256), 0, st, s->prim_bv, n, (const uint32_t*)s->bounds, ka, pa, s->hist, s->node_flags));
   (*launches)++;
   for (int p = 0; p < NPASS; p++) {
-    onesweep_kernel<KeyT, ITEMS><<<tiles, SORT_THREADS, TILE * (sizeof(KeyT) + ((RT_SORT_TMA && TILE * (sizeof(KeyT) + 4) <= 40 * 1024) ? 4 : 0)), st>>>(ka, kb, pa, pb, n, 8 * p, s->hist + 256 * p,
-                                                                                 s->lookback + (size_t)p * tiles * 256, s->tickets + p);
+    RT_CUDA(rt_launch_chained(rt_pdl_for(n), onesweep_kernel<KeyT, ITEMS>, dim3(tiles), dim3(SORT_THREADS), TILE * (sizeof(KeyT) + ((RT_SORT_TMA && TILE * (sizeof(KeyT) + 4) <= 40 * 1024) ? 4 : 0)), st,
+                              (const KeyT*)ka, kb, (const uint32_t*)pa, pb, n, 8 * p, (const uint32_t*)(s->hist + 256 * p), s->lookback + (size_t)p * tiles * 256, s->tickets + p));
     (*launches)++;
     KeyT* tk = ka; ka = kb; kb = tk;
     uint32_t* tp = pa; pa = pb; pb = tp;
@@ -342,7 +348,7 @@ int rt_build_codes_and_sort(rt_scene* s, int morton_bits, unsigned flags, cudaSt
   (*launches)++;
   if (flags & RT_BOUNDS_COMPUTED) {
     int g = (n + 255) / 256; if (g > 148 * 8) g = 148 * 8;
-    bounds_kernel<<<g, 256, 0, st>>>(s->prim_bv, n, (uint32_t*)s->bounds);
+    RT_CUDA(rt_launch_chained(rt_pdl_for(n), bounds_kernel, dim3(g), dim3(256), 0, st, (const float4*)s->prim_bv, n, (uint32_t*)s->bounds));
     (*launches)++;
   }
   RT_CUDA(cudaGetLastError());

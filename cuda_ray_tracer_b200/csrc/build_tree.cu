@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
                                                        const float4* __restrict__ bv, const float4* __restrict__ tv,
                                                        float4* __restrict__ sorted_tv, float4* nodes, int* flags, int n,
                                                        int* root_out, float* root_box) {
+  rt_pdl_wait();
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const uint32_t p = perm[k];
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(256) bottom_up_warp_kernel(const KeyT* __restr
                                                             const float4* __restrict__ bv, const float4* __restrict__ tv,
                                                             float4* __restrict__ sorted_tv, float4* nodes, int* flags, int n,
                                                             int* root_out, float* root_box, const int mode) {
+  rt_pdl_wait();  // last link of the build's chain (build.cuh): the sort's last pass must be complete
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31;
   const int k0 = k - (int)lane, klast = min(k0 + 31, n - 1);  // the warp's leaves
@@ -588,11 +590,11 @@ extern "C" int rt_build_lbvh(rt_scene* s, int morton_bits, unsigned flags, void*
     refit_kernel<<<grid, 256, 0, st>>>(s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->parent, s->node_flags, n, root_dev, root_box);
   } else if (!(flags & RT_BUILD_LOCAL_CLIMB)) {
     if (morton_bits == 30)
-      if (bu_mode == 0) bottom_up_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
-      else bottom_up_warp_kernel<uint32_t><<<grid, 256, 0, st>>>(s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits);
+      if (bu_mode == 0) RT_CUDA(rt_launch_chained(rt_pdl_for(n), bottom_up_kernel<uint32_t>, dim3(grid), dim3(256), 0, st, s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box));
+      else RT_CUDA(rt_launch_chained(rt_pdl_for(n), bottom_up_warp_kernel<uint32_t>, dim3(grid), dim3(256), 0, st, s->sorted_keys32, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits));
     else
-      if (bu_mode == 0) bottom_up_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box);
-      else bottom_up_warp_kernel<uint64_t><<<grid, 256, 0, st>>>(s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits);
+      if (bu_mode == 0) RT_CUDA(rt_launch_chained(rt_pdl_for(n), bottom_up_kernel<uint64_t>, dim3(grid), dim3(256), 0, st, s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box));
+      else RT_CUDA(rt_launch_chained(rt_pdl_for(n), bottom_up_warp_kernel<uint64_t>, dim3(grid), dim3(256), 0, st, s->sorted_keys64, s->sorted_perm, s->prim_bv, s->prim_tv, s->sorted_tv, s->nodes, s->node_flags, n, root_dev, root_box, bu_bits));
   } else {
     const int gl = (n + RT_BU_CHUNK - 1) / RT_BU_CHUNK;
     if (morton_bits == 30)

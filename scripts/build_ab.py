@@ -16,8 +16,8 @@ for n in (100_000, 1_000_000, 10_000_000):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     # climb variants of the fused builder: warp-first (default), every level global (round 1), and - timing only, no tree -
     # the leaf phase alone (RT_BU_LEAFONLY), which splits the kernel into gather/records and climb
-    for mode, fl, env in (("default", 0, None), ("no peek", 0, "RT_BU_NO_PEEK"), ("no compact", 0, "RT_BU_NO_COMPACT"), ("global", api.BUILD_GLOBAL_CLIMB, None), ("leaf-only", 0, "RT_BU_LEAFONLY")):
-        for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK"): os.environ.pop(e, None)
+    for mode, fl, env in (("default", 0, None), ("no pdl", 0, "RT_NO_PDL"), ("no peek", 0, "RT_BU_NO_PEEK"), ("no compact", 0, "RT_BU_NO_COMPACT"), ("global", api.BUILD_GLOBAL_CLIMB, None), ("leaf-only", 0, "RT_BU_LEAFONLY")):
+        for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK", "RT_NO_PDL"): os.environ.pop(e, None)
         if env: os.environ[env] = "1"
         for bits in (30, 63):
             ms = []
@@ -30,5 +30,5 @@ for n in (100_000, 1_000_000, 10_000_000):
                 warm.append(sc.build_lbvh_karas(bits, api.BOUNDS_COMPUTED | fl))
             print("%-6s %-12s n=%8d bits=%d  build after L2 flush: best %.3f median %.3f ms | right after update_triangles: best %.3f ms" % (
                 label, mode, n, bits, min(ms), statistics.median(ms), min(warm)))
-    for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK"): os.environ.pop(e, None)
+    for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK", "RT_NO_PDL"): os.environ.pop(e, None)
     sc.close(); del sc, a

@@ -118,3 +118,36 @@ def test_update_triangles_matches_host_setup():
     sc.build_lbvh_karas(30, api.BOUNDS_COMPUTED)
     e = sc.export_reference_layout(30)
     assert np.array_equal(e["perm"], b2["perm"]) and np.array_equal(e["bbox"].view(np.uint32), b2["bbox"].view(np.uint32))
+
+
+@pytest.mark.parametrize("bits", [30, 63])
+def test_rebuild_sequence_equals_fresh_builds(bits):
+    """A frame loop on ONE scene (update_triangles -> rt_build_lbvh, six frames of different vertices, no synchronisation in
+    between): every frame's tree equals the tree a fresh scene builds from the same vertices.  The build's kernels are
+    launched as a programmatic-dependent chain (csrc/build.cuh): blocks of the next kernel are resident while the previous
+    one finishes, so anything read before the dependency wait, or served from a stale cache line, would show here."""
+    n = 200_003
+    cfg, a = synth.soup(n, seed=21, width=32, height=32, aa=0)
+    a = synth.finish_triangles(a)
+    desc, keep = api.make_desc(cfg, a)
+    loop = api.Scene(desc, 0)
+    rng = np.random.RandomState(4)
+    for frame in range(6):
+        shift = rng.uniform(-0.3, 0.3, (n, 3)).astype(np.float32) * np.float32(frame > 0)
+        p0, p1, p2 = (np.ascontiguousarray(x + shift, np.float32) for x in a["tri"][:3])
+        loop.update_triangles(p0, p1, p2)
+        loop.build_lbvh_karas(bits, api.BOUNDS_COMPUTED, timed=False)
+        loop.update_triangles(p0, p1, p2)                      # and once more right behind it: the frame loop's back-to-back case
+        loop.build_lbvh_karas(bits, api.BOUNDS_COMPUTED, timed=False)
+        e = loop.export_reference_layout(bits)
+        cfg2, b = synth.soup(n, seed=21, width=32, height=32, aa=0)
+        b["tri"] = [p0, p1, p2] + list(api.triangle_setup(p0, p1, p2))
+        d2, k2 = api.make_desc(cfg2, b)
+        fresh = api.Scene(d2, 0)
+        fresh.build_lbvh_karas(bits, api.BOUNDS_COMPUTED | api.BUILD_TOPDOWN)
+        f = fresh.export_reference_layout(bits)
+        for key in ("codes", "perm", "left", "right"):
+            assert np.array_equal(e[key], f[key]), "frame %d: %s differs from a fresh build" % (frame, key)
+        assert np.array_equal(e["bbox"].view(np.uint32), f["bbox"].view(np.uint32)), "frame %d: boxes differ" % frame
+        fresh.close()
+    loop.close()
