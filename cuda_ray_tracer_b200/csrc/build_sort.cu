@@ -26,6 +26,13 @@ constexpr int SORT_THREADS = 256;
 #endif
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_VAL = (1u << 30) - 1;
+#ifndef RT_HIST_HYBRID
+#define RT_HIST_HYBRID 1  // 0: every digit through __match_any_sync (round 1), for A/B
+#endif
+#ifndef RT_LB_WINDOW
+#define RT_LB_WINDOW 8
+#endif
+constexpr int LB_WINDOW = RT_LB_WINDOW;
 
 // ---- state init: one launch instead of four memsets -------------------------------------------
 __global__ void init_build_state_kernel(uint32_t* hist, int hist_words, uint32_t* lookback, size_t lb_words, uint32_t* tickets,
@@ -126,11 +133,21 @@ __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ 
       keys[i] = code; perm[i] = (uint32_t)i; node_flags[i] = -1;
     }
     const unsigned act = __ballot_sync(0xffffffffu, valid);
+    if (act == 0u) continue;
+    const int first = __ffs(act) - 1;
 #pragma unroll
     for (int p = 0; p < NPASS; p++) {
       unsigned d = valid ? (unsigned)((code >> (8 * p)) & 0xFF) : 256u + lane;  // invalid lanes match nobody
-      unsigned peers = __match_any_sync(0xffffffffu, d) & act;
-      if (valid && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+      // Primitives in no particular order (the soup) have unrelated digits: 32 plain shared atomics, hardly a bank conflict,
+      // instead of one __match_any_sync round per digit (ncu r02: short_scoreboard 25 per issue, 37 of the build's 300 us).
+      // Digits that many lanes share - a mesh in file order, or every code equal as in the shipped reference - would
+      // serialise those atomics, so a warp whose first lane's digit is shared by more than 8 lanes aggregates first.
+      const unsigned d0 = __shfl_sync(0xffffffffu, d, first);  // every lane takes part: not inside the && below
+      const unsigned same = RT_HIST_HYBRID ? __ballot_sync(0xffffffffu, valid && d == d0) : 0xffffffffu;
+      if (__popc(same) > 8) {
+        const unsigned peers = __match_any_sync(0xffffffffu, d) & act;
+        if (valid && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+      } else if (valid) atomicAdd(&s_hist[p][d], 1u);
     }
   }
   __syncthreads();
@@ -262,13 +279,22 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
     const uint32_t lbase = oa + a - cnt, gdigit = ob + b - h;
     uint32_t excl = 0;
     if (tile > 0) {
+      // LB_WINDOW predecessors are read at once and then consumed in order: all tiles of a 1M sort are resident together,
+      // publish their aggregates at about the same time and then walk back until they meet an inclusive prefix; one
+      // dependent L2 read per predecessor made that walk the longest chain of the pass
       int t = (int)tile - 1;
-      while (true) {
-        uint32_t v = ld_volatile(lookback + (size_t)t * 256 + d);
-        if ((v >> 30) == 0) continue;  // predecessor has not published yet
-        excl += v & LB_VAL;
-        if (v & LB_INC) break;
-        t--;
+      bool done = false;
+      while (!done) {
+        uint32_t v[LB_WINDOW];
+#pragma unroll
+        for (int k = 0; k < LB_WINDOW; k++) v[k] = t - k >= 0 ? ld_volatile(lookback + (size_t)(t - k) * 256 + d) : LB_INC;
+#pragma unroll
+        for (int k = 0; k < LB_WINDOW; k++) {
+          if (done || (v[k] >> 30) == 0) break;  // not published yet: read again from here
+          excl += v[k] & LB_VAL;
+          t--;
+          done = (v[k] & LB_INC) != 0u;
+        }
       }
       st_volatile(lookback + (size_t)tile * 256 + d, LB_INC | (excl + cnt));
     }

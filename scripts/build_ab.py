@@ -16,7 +16,9 @@ for n in (100_000, 1_000_000, 10_000_000):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     # climb variants of the fused builder: warp-first (default), every level global (round 1), and - timing only, no tree -
     # the leaf phase alone (RT_BU_LEAFONLY), which splits the kernel into gather/records and climb
+    only = os.environ.get("BUILD_AB_MODES")  # e.g. "default" when comparing libraries (RT_LIB) rather than switches
     for mode, fl, env in (("default", 0, None), ("no pdl", 0, "RT_NO_PDL"), ("no peek", 0, "RT_BU_NO_PEEK"), ("no compact", 0, "RT_BU_NO_COMPACT"), ("global", api.BUILD_GLOBAL_CLIMB, None), ("leaf-only", 0, "RT_BU_LEAFONLY")):
+        if only and mode not in only.split(","): continue
         for e in ("RT_BU_LEAFONLY", "RT_BU_NO_COMPACT", "RT_BU_NO_PEEK", "RT_NO_PDL"): os.environ.pop(e, None)
         if env: os.environ[env] = "1"
         for bits in (30, 63):

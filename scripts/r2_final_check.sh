@@ -1,7 +1,9 @@
 #!/bin/bash
 # round-2 final check on one GPU: whole GPU suite (-x, the order the driver uses), smoke, default bench line, reference arm
+cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
-( time RT_REQUIRE_REF=1 timeout 1700 python -m pytest tests -m gpu -q -x -rs ) > gpurun_out/pytest_gpu_final.log 2>&1; tail -7 gpurun_out/pytest_gpu_final.log
+export PYTHONUNBUFFERED=1
+( time RT_REQUIRE_REF=1 timeout 600 python -m pytest tests -m gpu -q -x -rs --timeout 200 --timeout-method thread ) > gpurun_out/pytest_gpu_final.log 2>&1; tail -7 gpurun_out/pytest_gpu_final.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
 timeout 900 python bench.py > gpurun_out/bench_final.json 2> gpurun_out/bench_final.err; tail -c 300 gpurun_out/bench_final.err
 timeout 900 python bench.py --impl reference > gpurun_out/bench_ref_final.json 2> gpurun_out/bench_ref_final.err; tail -c 300 gpurun_out/bench_ref_final.err
@@ -15,4 +17,3 @@ for f in ("bench_final", "bench_ref_final"):
     except Exception as e:
         print(f, "FAILED", e)
 PY
-python scripts/slice_step_timing.py after_refill_fix 8 2>&1 | grep -v Warning
