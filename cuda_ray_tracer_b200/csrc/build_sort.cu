@@ -103,6 +103,27 @@ __device__ inline uint32_t quantize(float c, float mn, float range, float scale)
   return __float2uint_rz(nrm * scale);
 }
 
+// lanes of the (full) warp whose 8-bit digit equals mine.  MATCH.ANY resolves one distinct value after the other (about 30
+// of them among 32 random digits) and sat on 30 % of the pass's stall samples; eight ballots, one per bit, are independent
+// of each other and pipeline.  RT_RANK_BALLOT=0: the match instruction (round 1), for A/B.
+#ifndef RT_RANK_BALLOT
+#define RT_RANK_BALLOT 1
+#endif
+__device__ __forceinline__ unsigned rt_match_digit8(unsigned d) {
+#if RT_RANK_BALLOT
+  unsigned peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < 8; b++) {
+    const bool bit = (d >> b) & 1u;
+    const unsigned m = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+#else
+  return __match_any_sync(0xffffffffu, d);
+#endif
+}
+
 template <typename KeyT, int NPASS>
 __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ bv, int n, const uint32_t* __restrict__ bounds_enc,
                                                     KeyT* __restrict__ keys, uint32_t* __restrict__ perm, uint32_t* __restrict__ hist,
@@ -149,7 +170,7 @@ __global__ void __launch_bounds__(256) morton_kernel(const float4* __restrict__ 
       const unsigned d0 = __shfl_sync(0xffffffffu, d, first);  // every lane takes part: not inside the && below
       const unsigned same = RT_HIST_HYBRID ? __ballot_sync(0xffffffffu, valid && d == d0) : 0xffffffffu;
       if (__popc(same) > 8) {
-        const unsigned peers = __match_any_sync(0xffffffffu, d) & act;
+        const unsigned peers = rt_match_digit8(d) & act;  // (an invalid lane's low 8 bits may equal a valid digit: & act)
         if (valid && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
       } else if (valid) atomicAdd(&s_hist[p][d], 1u);
     }
@@ -257,7 +278,7 @@ __global__ void __launch_bounds__(SORT_THREADS) onesweep_kernel(const KeyT* __re
 #pragma unroll
     for (int b = 0; b < RANK_BATCH; b++) {
       dg[b] = (unsigned)((key[j0 + b] >> shift) & 0xFF);
-      peers[b] = __match_any_sync(0xffffffffu, dg[b]);
+      peers[b] = rt_match_digit8(dg[b]);
     }
 #pragma unroll
     for (int b = 0; b < RANK_BATCH; b++) {
