@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(256) bottom_up_kernel(const KeyT* __restrict__
 // 36 per issue: a warp stays resident until its last lane has finished a climb of dependent device-scope exchanges, and
 // most of that time most of its lanes are dead.  Here the 32 consecutive leaves of a warp first meet INSIDE the warp: in
 // every round each live lane (a finished subtree [l, r]) names its parent s and side exactly as above; two live lanes that
-// name the same parent are its two children (__match_any_sync), the left one takes the right one's half by shuffle, writes
+// name the same parent are its two children (the left one looks into the lane where its sibling must sit), the left one takes the right one's half by shuffle, writes
 // the finished 64-byte node and goes on with the union, the right one retires.  No flag, no atomic, no global read for a
 // node whose children both lie in the warp (about 26 of 31).  Rounds stop when none pairs up; what is left (subtrees whose
 // sibling reaches beyond the warp's 32 leaves) continues with the global protocol of bottom_up_kernel.  Same tree, same
@@ -174,12 +174,19 @@ __global__ void __launch_bounds__(256) bottom_up_warp_kernel(const KeyT* __restr
         need = false;
       }
     }
-    // the sibling can lie inside the warp only if it starts (side 0: at s + 1) or ends (side 1: at s) there
-    const bool cand = active && (side == 0 ? s + 1 <= klast : s >= k0);
-    const unsigned peers = __match_any_sync(0xffffffffu, cand ? (unsigned)s : (0x80000000u | lane));
-    const bool pair = cand && __popc(peers) == 2;
-    if (!__any_sync(0xffffffffu, pair)) break;
-    const int partner = pair ? (__ffs(peers & ~(1u << lane)) - 1) : (int)lane;
+    // A finished subtree [l, r] is always held by the lane of its leftmost leaf (the left child goes on, the right one
+    // retires), so the right sibling of a left child [l, s], if it is finished, sits in lane s + 1 - k0 and says so: a right
+    // child announces its parent.  One shuffle and one warp-wide OR per round; the MATCH.ANY this replaces resolves one
+    // distinct value after the other (see rt_match_digit8, build_sort.cu).
+    const bool left_cand = active && side == 0 && s + 1 <= klast;
+    const int want = left_cand ? s + 1 - k0 : (int)lane;
+    const int tag = (active && side == 1) ? s : -2;
+    const int ptag = __shfl_sync(0xffffffffu, tag, want);  // every lane takes part: not behind the && below
+    const bool pair_left = left_cand && ptag == s;
+    const unsigned taken = __reduce_or_sync(0xffffffffu, pair_left ? 1u << want : 0u);
+    if (taken == 0u) break;
+    const bool pair = pair_left || ((taken >> lane) & 1u);
+    const int partner = pair_left ? want : (int)lane;
     RtBox pb;
     pb.xmin = __shfl_sync(0xffffffffu, box.xmin, partner); pb.ymin = __shfl_sync(0xffffffffu, box.ymin, partner); pb.zmin = __shfl_sync(0xffffffffu, box.zmin, partner);
     pb.xmax = __shfl_sync(0xffffffffu, box.xmax, partner); pb.ymax = __shfl_sync(0xffffffffu, box.ymax, partner); pb.zmax = __shfl_sync(0xffffffffu, box.zmax, partner);
